@@ -1,0 +1,456 @@
+#!/usr/bin/env python
+"""bench.py -- the probe's headline measurement (BASELINE.json metric/config).
+
+One "step" = one pass of the pod's hot path over one GPU's buffer:
+    K1 triad  a = fma(3, c, b)   (24 B/element)  ->  K2 checksum_u64(a)  (8 B/element)
+    [N > 1]  + the 16-byte lanes exchange (the path's only collective)
+Workload = BASELINE.json configs[1]: 2^29 fp64 elements per array (4 GiB each) per GPU,
+generated on the device by K0.  `value` is whole-job GB/s of algorithmic bytes
+(32 B/element/step, summed over ranks) with everything resident in HBM; `e2e` is the
+same metric through gpu_probe_pipeline_run_host (pinned HOST b,c in, lanes out).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]           # this repo's CUDA path
+    python bench.py --impl reference ...                          # the CPU port (oracle/)
+
+torch is plumbing here: allocator, stream/events, torch.distributed.  Every compute
+call goes through the C ABI in lib/libgpuprobe.so (no fallback: a missing library or a
+failed launch raises).  oracle/ is used only as the checker and as the timed CPU arm.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "kind-gpu-sim_b200"))
+
+METRIC = "probe HBM GB/s/GPU + NVLink allreduce bus GB/s at 1/2/4/8 B200"
+FALLBACK_HBM_GBS = 6650.0  # /opt/skills/guides/B200_PROFILING.md fallback
+NVLINK_NOMINAL_GBS = 900.0
+BYTES_TRIAD, BYTES_CHECKSUM = 24, 8  # algorithmic bytes per element
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic():
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture."""
+    p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    try:
+        with open(p) as f:
+            return json.load(f)
+    except Exception:
+        return None
+
+
+def mem_available_bytes():
+    try:
+        with open("/proc/meminfo") as f:
+            for line in f:
+                if line.startswith("MemAvailable:"):
+                    return int(line.split()[1]) * 1024
+    except Exception:
+        pass
+    return 0
+
+
+class ClockSampler:
+    """Samples SM clock / throttle reasons of one GPU while the timed region runs."""
+
+    BAD = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+           "hw_power_brake_slowdown": 0x80}
+    NOTED = {"sw_power_cap": 0x4}
+
+    def __init__(self, index: int, period_s: float = 0.02):
+        self.index, self.period = index, period_s
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        self.err = None
+
+    def __enter__(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = self.index
+            if vis:
+                ids = [v for v in vis.split(",") if v != ""]
+                if self.index < len(ids) and ids[self.index].isdigit():
+                    idx = int(ids[self.index])
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+        except Exception as e:  # NVML missing: report it, do not invent clocks
+            self.err = f"{type(e).__name__}: {e}"
+        return self
+
+    def _run(self):
+        nv = self._nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append(int(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+                try:
+                    r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self._h))
+                except Exception:
+                    r = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h))
+                for name, bit in {**self.BAD, **self.NOTED}.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception as e:
+                self.err = f"{type(e).__name__}: {e}"
+                return
+            self._stop.wait(self.period)
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        if self._thr:
+            self._thr.join(timeout=2)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                    "samples": 0, "error": self.err or "no samples (timed region shorter than one period)"}
+        return {"sm_mhz": int(statistics.median(self.samples)), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# --------------------------------------------------------------------------------------
+# CPU arm: the oracle port timed on host cores (cpu_baseline leg and --impl reference)
+# --------------------------------------------------------------------------------------
+def cpu_pass_factory(n_sample: int):
+    import numpy as np
+    import oracle
+    b = oracle.init_fill(n_sample, 0, oracle.SEED_B)
+    c = oracle.init_fill(n_sample, 0, oracle.SEED_C)
+    a = np.empty_like(b)
+
+    def one_pass():
+        oracle.triad(b, c, 3.0, out=a)
+        return oracle.checksum_u64(a, 0)
+
+    return one_pass, oracle.max_threads()
+
+
+def cpu_baseline(n_sample: int, repeats: int = 3):
+    one_pass, cores = cpu_pass_factory(n_sample)
+    one_pass()  # first touch of a[]
+    best = float("inf")
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        one_pass()
+        best = min(best, time.perf_counter() - t0)
+    gbs = (BYTES_TRIAD + BYTES_CHECKSUM) * n_sample / best / 1e9
+    return {"value": round(gbs, 3), "unit": "GB/s", "cores": cores, "kind": "port",
+            "sample": f"oracle/probe_ref.c array mode, triad+checksum over 2^{n_sample.bit_length() - 1} fp64 elements "
+                      f"per array (of 2^29), best of {repeats}, OpenMP x{cores}"}
+
+
+def run_reference(args, rank: int):
+    """--impl reference: the reference has no implementation of this path (its slot is an
+    echo), so the CPU arm is the oracle port, all host threads, bounded sample per step."""
+    if rank != 0:
+        return
+    avail = mem_available_bytes()
+    while args.ref_log2n > 20 and avail and 3 * (8 << args.ref_log2n) > 0.5 * avail:
+        args.ref_log2n -= 1
+    n_sample = 1 << args.ref_log2n
+    one_pass, cores = cpu_pass_factory(n_sample)
+    for _ in range(max(args.warmup, 1)):
+        one_pass()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        one_pass()
+    dt = time.perf_counter() - t0
+    ms = dt / args.steps * 1e3
+    gbs = (BYTES_TRIAD + BYTES_CHECKSUM) * n_sample / (ms / 1e3) / 1e9
+    sample = (f"oracle/probe_ref.c array mode (CPU port; the reference's own slot is `echo`), triad+checksum over "
+              f"2^{args.ref_log2n} fp64 elements per array per step (bounded sample of the 2^29 workload), OpenMP x{cores}")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": round(gbs, 3), "unit": "GB/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 4), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64+u64", "data": "synthetic",
+        "config": workload_config(args, 1),
+        "cpu_baseline": {"value": round(gbs, 3), "unit": "GB/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": round(gbs, 3), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, world):
+    return {
+        "workload": "BASELINE.json configs[1]: 1-GPU probe pod, 4 GiB stream-triad + uint64 checksum vs CPU reference"
+                    + ("" if world == 1 else f" (replicated per GPU, {world} ranks; lanes exchanged every step)"),
+        "elements_per_gpu": 1 << args.log2n, "bytes_per_array_per_gpu": 8 << args.log2n,
+        "step": "triad(24 B/elem) + checksum_u64(8 B/elem)" + ("" if world == 1 else " + lanes allreduce(16 B)"),
+        "variant": args.variant,
+        "l2": "inputs are 3 x 4 GiB per GPU >> 126 MB L2, so no flush between iterations",
+        "parallelism": f"shard{world}" if world > 1 else "single",
+    }
+
+
+# --------------------------------------------------------------------------------------
+# GPU arm
+# --------------------------------------------------------------------------------------
+def run_ours(args, rank, local_rank, world):
+    import numpy as np
+    import torch
+
+    import gpuprobe
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the probe has no CPU fallback (use --impl reference for the CPU arm)")
+    gpuprobe.lib()  # raises if lib/libgpuprobe.so is missing
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    n = 1 << args.log2n
+    first = rank * n  # each rank owns the shard [rank*n, (rank+1)*n) of one global index space
+    variant = gpuprobe.VARIANTS[args.variant]
+    st = torch.cuda.current_stream().cuda_stream
+    b = torch.empty(n, dtype=torch.float64, device="cuda")
+    c = torch.empty(n, dtype=torch.float64, device="cuda")
+    a = torch.empty(n, dtype=torch.float64, device="cuda")
+    ws = torch.zeros(gpuprobe.workspace_bytes() // 8, dtype=torch.int64, device="cuda")
+    lanes = torch.zeros(2, dtype=torch.int64, device="cuda")
+    total = torch.zeros(2, dtype=torch.int64, device="cuda")
+    gpuprobe.init_fill(b.data_ptr(), n, first, gpuprobe.SEED_B, st)
+    gpuprobe.init_fill(c.data_ptr(), n, first, gpuprobe.SEED_C, st)
+    torch.cuda.synchronize()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    def step(ev=None):
+        if ev:
+            ev[0].record()
+        gpuprobe.triad(a.data_ptr(), b.data_ptr(), c.data_ptr(), gpuprobe.SCALAR, n, variant, st)
+        if ev:
+            ev[1].record()
+        gpuprobe.checksum_u64(a.data_ptr(), n, first, lanes.data_ptr(), ws.data_ptr(), variant, st)
+        if ev:
+            ev[2].record()
+        if dist is not None:  # wrapping int64 sum == wrapping u64 sum, bit for bit
+            total.copy_(lanes)
+            dist.all_reduce(total)
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    torch.cuda.synchronize()
+    with ClockSampler(local_rank) as clk:
+        t_start.record()
+        for k in range(args.steps):
+            step(evs[k])
+        t_end.record()
+        torch.cuda.synchronize()
+    barrier()
+    ms_total = t_start.elapsed_time(t_end)
+    triad_ms = [e[0].elapsed_time(e[1]) for e in evs]
+    csum_ms = [e[1].elapsed_time(e[2]) for e in evs]
+    my_lanes = tuple(int(x) for x in lanes.cpu().numpy().view(np.uint64))
+
+    if dist is not None:
+        t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    ms_step = ms_total / args.steps
+    step_bytes = (BYTES_TRIAD + BYTES_CHECKSUM) * n * world
+    value = step_bytes / (ms_step / 1e3) / 1e9
+
+    # ---- end to end: pinned host b,c -> device -> lanes back, through the pipeline ABI ----
+    e2e = run_e2e(args, gpuprobe, torch, b, c, n, first, my_lanes, dist, world)
+
+    # ---- NVLink part of the metric (N > 1): allreduce sweep, bus bandwidth ----
+    nvlink = run_allreduce_sweep(args, torch, dist, world) if dist is not None else None
+
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        t_avg = sum(triad_ms) / len(triad_ms)
+        c_avg = sum(csum_ms) / len(csum_ms)
+        ach = BYTES_TRIAD * n / (t_avg / 1e3) / 1e9
+        traffic = ncu_traffic()
+        line = {
+            "metric": METRIC, "value": round(value, 2), "unit": "GB/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64+u64", "data": "synthetic", "config": workload_config(args, world),
+            "roofline": {
+                "bound": "hbm", "kernel": "triad", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
+                "frac": round(ach / peak, 4), "peak_source": peak_src, "frac_of_nominal_8000": round(ach / 8000.0, 4),
+                "traffic": (traffic or {}).get("triad_dram_bytes_per_launch"),
+                "algorithmic_bytes_per_launch": BYTES_TRIAD * n,
+                "avg_launch_ms": round(t_avg, 4), "best_launch_ms": round(min(triad_ms), 4),
+            },
+            "kernels": {
+                "triad": {"bytes": BYTES_TRIAD * n, "avg_ms": round(t_avg, 4), "best_ms": round(min(triad_ms), 4),
+                          "GBps_avg": round(ach, 1), "frac_measured_peak": round(ach / peak, 4)},
+                "checksum_u64": {"bytes": BYTES_CHECKSUM * n, "avg_ms": round(c_avg, 4),
+                                 "best_ms": round(min(csum_ms), 4),
+                                 "GBps_avg": round(BYTES_CHECKSUM * n / (c_avg / 1e3) / 1e9, 1),
+                                 "frac_measured_peak": round(BYTES_CHECKSUM * n / (c_avg / 1e3) / 1e9 / peak, 4)},
+            },
+            "clocks": clk.summary(),
+            "e2e": e2e,
+            "gpu_launches": 2 * args.steps,
+            "lanes": [f"0x{my_lanes[0]:016x}", f"0x{my_lanes[1]:016x}"],
+        }
+        if nvlink is not None:
+            line["nvlink"] = nvlink
+        if world == 1 and not args.no_cpu:
+            import oracle
+            want = oracle.stream_lanes(n, first)
+            line["parity"] = {"gpu_lanes_equal_cpu_oracle": want == my_lanes, "checked": f"2^{args.log2n} elements"}
+            avail = mem_available_bytes()
+            log2s = args.cpu_log2n
+            while log2s > 20 and avail and 3 * (8 << log2s) > 0.5 * avail:
+                log2s -= 1
+            line["cpu_baseline"] = cpu_baseline(1 << log2s)
+            if want != my_lanes:
+                print(json.dumps(line), flush=True)
+                raise SystemExit("bench.py: GPU lanes differ from the CPU oracle")
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def run_e2e(args, gpuprobe, torch, b, c, n, first, want_lanes, dist, world):
+    """Same step through the host-buffer ABI.  Inputs start in pinned HOST memory every
+    step (untimed setup copies them out of the device buffers K0 filled)."""
+    log2e = min(args.e2e_log2n, args.log2n)
+    avail = mem_available_bytes()
+    while log2e > 20 and avail and world * 2 * (8 << log2e) > 0.4 * avail:
+        log2e -= 1
+    ne = 1 << log2e
+    hb = torch.empty(ne, dtype=torch.float64).pin_memory()
+    hc = torch.empty(ne, dtype=torch.float64).pin_memory()
+    hb.copy_(b[:ne])
+    hc.copy_(c[:ne])
+    torch.cuda.synchronize()
+    pipe = gpuprobe.Pipeline(0, 0)
+    try:
+        for _ in range(max(1, args.e2e_warmup)):
+            got = pipe.run_host(hb.data_ptr(), hc.data_ptr(), None, gpuprobe.SCALAR, ne, first)
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(args.e2e_steps):
+            got = pipe.run_host(hb.data_ptr(), hc.data_ptr(), None, gpuprobe.SCALAR, ne, first)  # blocking
+        dt = time.perf_counter() - t0
+    finally:
+        pipe.close()
+    if ne == n and got != want_lanes:
+        raise SystemExit(f"bench.py: e2e lanes {got} differ from the resident path {want_lanes}")
+    ms = dt / args.e2e_steps * 1e3
+    if dist is not None:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    gbs = (BYTES_TRIAD + BYTES_CHECKSUM) * ne * world / (ms / 1e3) / 1e9
+    return {"value": round(gbs, 2), "unit": "GB/s", "h2d_bytes_per_step": 16 * ne, "d2h_bytes_per_step": 16,
+            "ms_per_step": round(ms, 3), "steps": args.e2e_steps, "elements_per_gpu": ne,
+            "api": "gpu_probe_pipeline_run_host (pinned host b,c -> chunked H2D overlapped with fused "
+                   "triad+checksum -> lanes D2H); host wall clock around blocking calls",
+            "pcie_h2d_GBps": round(16 * ne / (ms / 1e3) / 1e9, 2)}
+
+
+def run_allreduce_sweep(args, torch, dist, world):
+    """In-place fp32 sum allreduce, 1 KiB .. 1 GiB per rank; busbw = algbw * 2(G-1)/G."""
+    rank = dist.get_rank()
+    max_bytes = 1 << args.sweep_log2max
+    buf = torch.ones(max_bytes // 4, dtype=torch.float32, device="cuda")
+    rows = []
+    size = 1 << 10
+    while size <= max_bytes:
+        view = buf[: size // 4]
+        iters = 20 if size >= (1 << 20) else 50
+        for _ in range(5):
+            dist.all_reduce(view)
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            dist.all_reduce(view)
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        algbw = size / (ms / 1e3) / 1e9
+        rows.append({"bytes": size, "us": round(ms * 1e3, 2), "algbw_GBps": round(algbw, 2),
+                     "busbw_GBps": round(algbw * 2 * (world - 1) / world, 2)})
+        buf.fill_(1.0)
+        size <<= 1
+    top = rows[-1]
+    best = max(rows, key=lambda r: r["busbw_GBps"])
+    return {"collective": "NCCL allreduce fp32 sum in place (torch.distributed), max over ranks",
+            "busbw_GBps_at_max": top["busbw_GBps"], "max_bytes": top["bytes"],
+            "busbw_GBps_peak": best["busbw_GBps"], "peak_bytes": best["bytes"],
+            "frac_of_nominal_900": round(top["busbw_GBps"] / NVLINK_NOMINAL_GBS, 4),
+            "latency_us_1KiB": rows[0]["us"], "sweep": rows} if rank == 0 else None
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--log2n", type=int, default=29, help="fp64 elements per array per GPU (29 = BASELINE 4 GiB)")
+    ap.add_argument("--variant", choices=["auto", "ldg128", "tma", "ldg256"], default="auto")
+    ap.add_argument("--e2e-log2n", type=int, default=29)
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--e2e-warmup", type=int, default=1)
+    ap.add_argument("--cpu-log2n", type=int, default=28, help="cpu_baseline sample size (elements per array)")
+    ap.add_argument("--ref-log2n", type=int, default=28, help="--impl reference sample per step")
+    ap.add_argument("--sweep-log2max", type=int, default=30)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / parity leg")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3  # timing rule: at least 3 warm-up steps
+    rank, local_rank, world = env_int("RANK", 0), env_int("LOCAL_RANK", 0), env_int("WORLD_SIZE", 1)
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit(f"bench.py: --gpus {args.gpus} needs torchrun (one rank per GPU); see the docstring")
+        args.gpus = world
+    run_ours(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,121 @@
+/*
+ * include/gpu_probe.h -- C ABI of the B200 validation probe (libgpuprobe.so).
+ *
+ * What this boundary replaces.  The reference (maryamtahhan/kind-gpu-sim) has no
+ * FFI and no compute: a GPU-requesting pod runs
+ *     /root/reference/pods/nvidia-gpu-test-pod.yaml:9    echo ... && sleep 3600
+ * after the scheduler matched `limits nvidia.com/gpu` (same file :10-12) against
+ * the capacity that /root/reference/kind-gpu-sim.sh:114-116 advertises.  The probe
+ * fills that container-command slot with real work.  The entry points below are
+ * what a host in the reference's own toolchain (bash -> a small C binary, see
+ * kind-gpu-sim_b200/host/gpu_probe_main.c) binds; SURVEY.md section 8(b) lists
+ * them.  Each comment names the reference line whose slot the call fills.
+ *
+ * Conventions
+ *  - plain C: pointers, sizes, no CUDA/torch types.  `stream` is a cudaStream_t
+ *    passed as void* (NULL = the legacy default stream).
+ *  - every pointer called "device" must be device memory of the CURRENT device,
+ *    8-byte aligned; 16-byte alignment enables the vector/TMA paths (cudaMalloc
+ *    gives 256).  The caller owns every buffer; nothing here allocates unless
+ *    its comment says so.
+ *  - all calls are asynchronous on `stream` unless marked [blocking].
+ *  - return value: 0 = ok; > 0 = cudaError_t; -1..-99 = -(ncclResult_t);
+ *    <= -100 = GPU_PROBE_E* below.  gpu_probe_error_string() explains any of them.
+ *  - there is NO CPU fallback: on a machine without an sm_100 GPU every compute
+ *    entry point returns a CUDA error.
+ */
+#ifndef GPU_PROBE_H
+#define GPU_PROBE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GPU_PROBE_ABI_VERSION 1
+
+/* Spec constants. */
+#define GPU_PROBE_SEED_B 0x0123456789ABCDEFull
+#define GPU_PROBE_SEED_C 0xFEDCBA9876543210ull
+#define GPU_PROBE_SCALAR 3.0
+
+/* Kernel variants (how a streaming kernel moves its bytes). */
+#define GPU_PROBE_VARIANT_AUTO (-1) /* the variant measured fastest on B200      */
+#define GPU_PROBE_VARIANT_LDG 0     /* 128-bit coalesced ld/st, streaming hints   */
+#define GPU_PROBE_VARIANT_TMA 1     /* cp.async.bulk + mbarrier smem ring         */
+#define GPU_PROBE_VARIANT_LDG256 2  /* 256-bit ld/st (sm_100 v4.b64)              */
+
+/* Probe-level errors (<= -100). */
+#define GPU_PROBE_EINVAL (-100)    /* null pointer, bad variant, bad size         */
+#define GPU_PROBE_EALIGN (-101)    /* pointer not 8-byte aligned                  */
+#define GPU_PROBE_ETOOBIG (-102)   /* size beyond a stated maximum                */
+#define GPU_PROBE_ENOTREADY (-103) /* object used before create / after destroy   */
+
+int gpu_probe_abi_version(void);
+
+/* Static description: arch, variants compiled in.  Never NULL. */
+const char *gpu_probe_kernel_info(void);
+
+/* Text for any return value of this library.  Never NULL. */
+const char *gpu_probe_error_string(int rc);
+
+/* K0  dst[k] = (double)(splitmix64(first_index + k, seed) >> 11) * 2^-53.
+ * Synthetic input generated on the device: the pod has no input to copy
+ * (slot: pods/nvidia-gpu-test-pod.yaml:9; spec: SURVEY 8d "Generator"). */
+int gpu_probe_init_fill(double *dst, uint64_t n, uint64_t first_index,
+                        uint64_t seed, void *stream);
+
+/* K1  a[k] = fma(s, c[k], b[k]), one rounding.  24 bytes of HBM traffic per
+ * element.  (slot: pods/nvidia-gpu-test-pod.yaml:9; spec: SURVEY 8d "Triad") */
+int gpu_probe_triad(double *a, const double *b, const double *c, double s,
+                    uint64_t n, int variant, void *stream);
+
+/* Bytes of device scratch the checksum kernels need (a constant). */
+size_t gpu_probe_checksum_workspace_bytes(void);
+
+/* K2  out_lanes[0] = sum w[k], out_lanes[1] = sum w[k]*(2*(first_index+k)+1),
+ * both mod 2^64.  One launch; out_lanes (device, 2 words) is overwritten.
+ * `workspace` is device scratch of gpu_probe_checksum_workspace_bytes() bytes,
+ * zeroed ONCE by the caller after allocation (the kernel leaves it zeroed);
+ * calls that overlap on the GPU must not share a workspace.
+ * (slot: pods/nvidia-gpu-test-pod.yaml:9; spec: SURVEY 8d "Checksum") */
+int gpu_probe_checksum_u64(const uint64_t *w, uint64_t n, uint64_t first_index,
+                           uint64_t *out_lanes, void *workspace, int variant,
+                           void *stream);
+
+/* K1+K2 fused: writes a[] and the lanes of a[] in one pass (24 B/element instead
+ * of 32).  Same lanes as gpu_probe_triad followed by gpu_probe_checksum_u64.
+ *  */
+int gpu_probe_triad_checksum(double *a, const double *b, const double *c,
+                             double s, uint64_t n, uint64_t first_index,
+                             uint64_t *out_lanes, void *workspace, int variant,
+                             void *stream);
+
+/* K3  SM-driven copy dst[k] = src[k]; dst and/or src may be a peer GPU's memory
+ * once peer access is enabled (NVLink 5 path).  bytes need not be a multiple of
+ * 16.  (spec: SURVEY 8d "P2P copy") */
+int gpu_probe_p2p_copy(void *dst, const void *src, uint64_t bytes, void *stream);
+
+/* ---- host-buffer pipeline (the end-to-end call for a host that holds b, c) ----
+ * create [blocking, ALLOCATES]: device staging for `depth` chunks of
+ * `chunk_elems` doubles x3 arrays, two streams, events -- on the current device.
+ * run_host [blocking]: streams pinned host b,c through the device in chunks
+ * (H2D overlapped with the fused triad+checksum kernel), optionally copies a[]
+ * back, and returns the lanes in host memory.  Host buffers should be pinned
+ * (cudaHostAlloc / cudaHostRegister) or the copies serialise. */
+typedef struct gpu_probe_pipeline gpu_probe_pipeline;
+
+int gpu_probe_pipeline_create(gpu_probe_pipeline **out, uint64_t chunk_elems,
+                              int depth);
+int gpu_probe_pipeline_run_host(gpu_probe_pipeline *p, const double *b_host,
+                                const double *c_host, double *a_host_or_null,
+                                double s, uint64_t n, uint64_t first_index,
+                                uint64_t lanes_out_host[2]);
+int gpu_probe_pipeline_destroy(gpu_probe_pipeline *p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPU_PROBE_H */

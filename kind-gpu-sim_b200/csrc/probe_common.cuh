@@ -1,0 +1,150 @@
+// probe_common.cuh -- device helpers shared by the probe kernels (sm_100a only).
+//
+// Spec: SURVEY.md section 8(d).  No reference counterpart exists: the slot these
+// kernels fill is the container command at
+// /root/reference/pods/nvidia-gpu-test-pod.yaml:9.
+#pragma once
+
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace probe {
+
+// ---- spec arithmetic --------------------------------------------------------
+__host__ __device__ __forceinline__ uint64_t splitmix64_at(uint64_t i, uint64_t seed) {
+  uint64_t z = seed + (i + 1) * 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+
+__device__ __forceinline__ double unit_double(uint64_t x) {
+  // 53-bit integer -> double is exact; the power-of-two scale is exact.
+  return __ull2double_rn(x >> 11) * 0x1.0p-53;
+}
+
+// ---- streaming global accesses ----------------------------------------------
+// Everything on this path is touched once, so nothing may displace useful lines.
+// 128-bit forms use .cs (evict-first in L1 and L2: SASS LDG.E.EF.128); the 256-bit
+// forms are sm_100+ (LDG.E.NA.EFL2.256) -- ptxas accepts .L2::evict_first on ld
+// only for the 256-bit types.
+struct alignas(16) f64x2 { double x, y; };
+struct alignas(32) f64x4 { double x, y, z, w; };
+struct alignas(16) u64x2 { uint64_t x, y; };
+struct alignas(32) u64x4 { uint64_t x, y, z, w; };
+
+__device__ __forceinline__ f64x2 ld_stream(const f64x2 *p) {
+  f64x2 v;
+  asm volatile("ld.global.cs.v2.f64 {%0,%1}, [%2];"
+               : "=d"(v.x), "=d"(v.y) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ f64x4 ld_stream(const f64x4 *p) {
+  f64x4 v;
+  asm volatile("ld.global.L1::no_allocate.L2::evict_first.v4.f64 {%0,%1,%2,%3}, [%4];"
+               : "=d"(v.x), "=d"(v.y), "=d"(v.z), "=d"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ u64x2 ld_stream(const u64x2 *p) {
+  u64x2 v;
+  asm volatile("ld.global.cs.v2.u64 {%0,%1}, [%2];"
+               : "=l"(v.x), "=l"(v.y) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ u64x4 ld_stream(const u64x4 *p) {
+  u64x4 v;
+  asm volatile("ld.global.L1::no_allocate.L2::evict_first.v4.u64 {%0,%1,%2,%3}, [%4];"
+               : "=l"(v.x), "=l"(v.y), "=l"(v.z), "=l"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void st_stream(f64x2 *p, const f64x2 &v) {
+  asm volatile("st.global.cs.v2.f64 [%0], {%1,%2};"
+               :: "l"(p), "d"(v.x), "d"(v.y) : "memory");
+}
+__device__ __forceinline__ void st_stream(f64x4 *p, const f64x4 &v) {
+  asm volatile("st.global.L1::no_allocate.v4.f64 [%0], {%1,%2,%3,%4};"
+               :: "l"(p), "d"(v.x), "d"(v.y), "d"(v.z), "d"(v.w) : "memory");
+}
+__device__ __forceinline__ void st_stream(u64x2 *p, const u64x2 &v) {
+  asm volatile("st.global.cs.v2.u64 [%0], {%1,%2};"
+               :: "l"(p), "l"(v.x), "l"(v.y) : "memory");
+}
+__device__ __forceinline__ void st_stream(u64x4 *p, const u64x4 &v) {
+  asm volatile("st.global.L1::no_allocate.v4.u64 [%0], {%1,%2,%3,%4};"
+               :: "l"(p), "l"(v.x), "l"(v.y), "l"(v.z), "l"(v.w) : "memory");
+}
+
+// ---- lanes ------------------------------------------------------------------
+struct Lanes {
+  uint64_t s0, s1;
+  __device__ __forceinline__ void add(uint64_t w, uint64_t m) { s0 += w; s1 += w * m; }
+};
+
+__device__ __forceinline__ Lanes warp_sum(Lanes v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    v.s0 += __shfl_xor_sync(0xffffffffu, v.s0, o);
+    v.s1 += __shfl_xor_sync(0xffffffffu, v.s1, o);
+  }
+  return v;
+}
+
+// Block sum; result valid in thread 0.  `smem` holds 2*32 words.
+__device__ __forceinline__ Lanes block_sum(Lanes v, uint64_t *smem) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nwarps = (blockDim.x + 31) >> 5;
+  v = warp_sum(v);
+  if (lane == 0) { smem[2 * warp] = v.s0; smem[2 * warp + 1] = v.s1; }
+  __syncthreads();
+  if (warp == 0) {
+    Lanes t{0, 0};
+    if (lane < nwarps) { t.s0 = smem[2 * lane]; t.s1 = smem[2 * lane + 1]; }
+    v = warp_sum(t);
+  }
+  __syncthreads();  // smem reusable afterwards
+  return v;
+}
+
+// Workspace layout (device scratch, see gpu_probe_checksum_workspace_bytes):
+//   word 0            : ticket counter (zero between launches)
+//   words 32 ..       : per-CTA partial lanes, 2 words per CTA
+constexpr int kMaxPartialCtas = 4096;
+constexpr int kPartialsOffsetWords = 32;  // keep the ticket on its own 256-B line
+constexpr size_t kWorkspaceBytes =
+    sizeof(uint64_t) * (kPartialsOffsetWords + 2 * size_t(kMaxPartialCtas));
+
+// Every CTA publishes its partial; the last one to take a ticket adds them up,
+// applies the global-index fix-up and overwrites out[0..1].  Wrapping u64 sums are
+// associative and commutative, so the order CTAs finish in cannot change a bit.
+//   lane1 was accumulated with LOCAL indices k; sum w*(2(f+k)+1) = lane1 + 2f*lane0.
+__device__ __forceinline__ void finish_lanes(Lanes mine, uint64_t first_index,
+                                             uint64_t *__restrict__ out,
+                                             uint64_t *__restrict__ ws, uint64_t *smem) {
+  __shared__ bool is_last;
+  Lanes blk = block_sum(mine, smem);
+  if (threadIdx.x == 0) {
+    uint64_t *part = ws + kPartialsOffsetWords + 2 * size_t(blockIdx.x);
+    __stcg(part, blk.s0);
+    __stcg(part + 1, blk.s1);
+    __threadfence();
+    unsigned long long t = atomicAdd(reinterpret_cast<unsigned long long *>(ws), 1ull);
+    is_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  Lanes acc{0, 0};
+  for (unsigned i = threadIdx.x; i < gridDim.x; i += blockDim.x) {
+    const uint64_t *part = ws + kPartialsOffsetWords + 2 * size_t(i);
+    acc.s0 += __ldcg(part);
+    acc.s1 += __ldcg(part + 1);
+  }
+  acc = block_sum(acc, smem);
+  if (threadIdx.x == 0) {
+    out[0] = acc.s0;
+    out[1] = acc.s1 + 2 * first_index * acc.s0;
+    ws[0] = 0;  // ticket back to zero for the next launch on this workspace
+  }
+}
+
+}  // namespace probe

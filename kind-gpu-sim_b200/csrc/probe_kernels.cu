@@ -1,0 +1,600 @@
+// probe_kernels.cu -- the probe's sm_100a kernels and their C ABI (include/gpu_probe.h).
+//
+// K0 init_fill, K1 triad, K2 checksum_u64, K1+K2 fused, K3 p2p copy.  All are
+// HBM- (or NVLink-) bound byte movers: one FMA or ~6 integer ops per 8-byte word,
+// so the design is about bytes in flight, coalescing and grid size, not math.
+//   * LDG variants: 128-/256-bit coalesced streaming loads, U independent loads
+//     per array per thread issued before first use, persistent grid-stride CTAs.
+//   * TMA variants: one elected thread feeds a ring of shared-memory stages with
+//     1-D bulk async copies (UBLKCP) tracked by mbarriers; the CTA's threads
+//     consume from shared memory; results leave through bulk stores.
+// No reference counterpart (the slot is /root/reference/pods/nvidia-gpu-test-pod.yaml:9);
+// spec: SURVEY.md section 8(d).  There is no CPU path in this file.
+#include "gpu_probe.h"
+
+#include <atomic>
+#include <cstdio>
+#include <cuda_runtime.h>
+
+#include "probe_common.cuh"
+#include "probe_tma.cuh"
+
+namespace probe {
+
+constexpr int kThreads = 256;
+
+// ---------------------------------------------------------------------------
+// vector helpers
+// ---------------------------------------------------------------------------
+template <typename V> struct lanes_of { static constexpr int E = int(sizeof(V) / 8); };
+
+__device__ __forceinline__ f64x2 fma_vec(double s, const f64x2 &c, const f64x2 &b) {
+  return f64x2{__fma_rn(s, c.x, b.x), __fma_rn(s, c.y, b.y)};
+}
+__device__ __forceinline__ f64x4 fma_vec(double s, const f64x4 &c, const f64x4 &b) {
+  return f64x4{__fma_rn(s, c.x, b.x), __fma_rn(s, c.y, b.y), __fma_rn(s, c.z, b.z), __fma_rn(s, c.w, b.w)};
+}
+__device__ __forceinline__ uint64_t bits(double x) { return uint64_t(__double_as_longlong(x)); }
+
+// k0 = LOCAL index of the vector's first word; multiplier of word k is 2k+1.
+__device__ __forceinline__ void lanes_vec(Lanes &acc, const f64x2 &v, uint64_t k0) {
+  const uint64_t m = 2 * k0 + 1;
+  acc.add(bits(v.x), m); acc.add(bits(v.y), m + 2);
+}
+__device__ __forceinline__ void lanes_vec(Lanes &acc, const f64x4 &v, uint64_t k0) {
+  const uint64_t m = 2 * k0 + 1;
+  acc.add(bits(v.x), m); acc.add(bits(v.y), m + 2); acc.add(bits(v.z), m + 4); acc.add(bits(v.w), m + 6);
+}
+__device__ __forceinline__ void lanes_vec(Lanes &acc, const u64x2 &v, uint64_t k0) {
+  const uint64_t m = 2 * k0 + 1;
+  acc.add(v.x, m); acc.add(v.y, m + 2);
+}
+__device__ __forceinline__ void lanes_vec(Lanes &acc, const u64x4 &v, uint64_t k0) {
+  const uint64_t m = 2 * k0 + 1;
+  acc.add(v.x, m); acc.add(v.y, m + 2); acc.add(v.z, m + 4); acc.add(v.w, m + 6);
+}
+
+// ---------------------------------------------------------------------------
+// K0  init_fill
+// ---------------------------------------------------------------------------
+template <int U>
+__global__ void __launch_bounds__(kThreads)
+init_fill_vec(f64x2 *__restrict__ dst, uint64_t nvec, uint64_t n, uint64_t first, uint64_t seed) {
+  const uint64_t tile = uint64_t(kThreads) * U;
+  for (uint64_t base = blockIdx.x * tile; base < nvec; base += gridDim.x * tile) {
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint64_t idx = base + uint64_t(u) * kThreads + threadIdx.x;
+      if (idx < nvec) {
+        const uint64_t k = first + 2 * idx;
+        st_stream(dst + idx, f64x2{unit_double(splitmix64_at(k, seed)), unit_double(splitmix64_at(k + 1, seed))});
+      }
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && (n & 1))
+    reinterpret_cast<double *>(dst)[n - 1] = unit_double(splitmix64_at(first + n - 1, seed));
+}
+
+__global__ void __launch_bounds__(kThreads)
+init_fill_scalar(double *__restrict__ dst, uint64_t n, uint64_t first, uint64_t seed) {
+  for (uint64_t k = blockIdx.x * uint64_t(kThreads) + threadIdx.x; k < n; k += uint64_t(gridDim.x) * kThreads)
+    dst[k] = unit_double(splitmix64_at(first + k, seed));
+}
+
+// ---------------------------------------------------------------------------
+// K1 / K1+K2  triad, LDG variants
+// ---------------------------------------------------------------------------
+template <typename V, int U, bool LANES>
+__global__ void __launch_bounds__(kThreads)
+triad_vec(V *__restrict__ a, const V *__restrict__ b, const V *__restrict__ c, double s, uint64_t nvec,
+          uint64_t n, uint64_t first, uint64_t *__restrict__ out, uint64_t *__restrict__ ws) {
+  constexpr int E = lanes_of<V>::E;
+  __shared__ uint64_t red[64];
+  Lanes acc{0, 0};
+  const uint64_t tile = uint64_t(kThreads) * U;
+  for (uint64_t base = blockIdx.x * tile; base < nvec; base += gridDim.x * tile) {
+    const uint64_t i0 = base + threadIdx.x;
+    V vb[U], vc[U];
+    if (base + tile <= nvec) {  // full tile: every load issued before any use
+#pragma unroll
+      for (int u = 0; u < U; ++u) vb[u] = ld_stream(b + i0 + uint64_t(u) * kThreads);
+#pragma unroll
+      for (int u = 0; u < U; ++u) vc[u] = ld_stream(c + i0 + uint64_t(u) * kThreads);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const uint64_t idx = i0 + uint64_t(u) * kThreads;
+        const V r = fma_vec(s, vc[u], vb[u]);
+        st_stream(a + idx, r);
+        if (LANES) lanes_vec(acc, r, idx * E);
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const uint64_t idx = i0 + uint64_t(u) * kThreads;
+        if (idx < nvec) {
+          const V r = fma_vec(s, ld_stream(c + idx), ld_stream(b + idx));
+          st_stream(a + idx, r);
+          if (LANES) lanes_vec(acc, r, idx * E);
+        }
+      }
+    }
+  }
+  // scalar tail: fewer than E elements
+  const uint64_t done = nvec * E;
+  if (blockIdx.x == gridDim.x - 1 && threadIdx.x < n - done) {
+    const uint64_t k = done + threadIdx.x;
+    const double r = __fma_rn(s, reinterpret_cast<const double *>(c)[k], reinterpret_cast<const double *>(b)[k]);
+    reinterpret_cast<double *>(a)[k] = r;
+    if (LANES) acc.add(bits(r), 2 * k + 1);
+  }
+  if (LANES) finish_lanes(acc, first, out, ws, red);
+}
+
+template <bool LANES>
+__global__ void __launch_bounds__(kThreads)
+triad_scalar(double *__restrict__ a, const double *__restrict__ b, const double *__restrict__ c, double s,
+             uint64_t n, uint64_t first, uint64_t *__restrict__ out, uint64_t *__restrict__ ws) {
+  __shared__ uint64_t red[64];
+  Lanes acc{0, 0};
+  for (uint64_t k = blockIdx.x * uint64_t(kThreads) + threadIdx.x; k < n; k += uint64_t(gridDim.x) * kThreads) {
+    const double r = __fma_rn(s, c[k], b[k]);
+    a[k] = r;
+    if (LANES) acc.add(bits(r), 2 * k + 1);
+  }
+  if (LANES) finish_lanes(acc, first, out, ws, red);
+}
+
+// ---------------------------------------------------------------------------
+// K2  checksum, LDG variants
+// ---------------------------------------------------------------------------
+template <typename V, int U>
+__global__ void __launch_bounds__(kThreads)
+checksum_vec(const V *__restrict__ w, uint64_t nvec, uint64_t n, uint64_t first, uint64_t *__restrict__ out,
+             uint64_t *__restrict__ ws) {
+  constexpr int E = lanes_of<V>::E;
+  __shared__ uint64_t red[64];
+  Lanes acc{0, 0};
+  const uint64_t tile = uint64_t(kThreads) * U;
+  for (uint64_t base = blockIdx.x * tile; base < nvec; base += gridDim.x * tile) {
+    const uint64_t i0 = base + threadIdx.x;
+    if (base + tile <= nvec) {
+      V v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) v[u] = ld_stream(w + i0 + uint64_t(u) * kThreads);
+#pragma unroll
+      for (int u = 0; u < U; ++u) lanes_vec(acc, v[u], (i0 + uint64_t(u) * kThreads) * E);
+    } else {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const uint64_t idx = i0 + uint64_t(u) * kThreads;
+        if (idx < nvec) lanes_vec(acc, ld_stream(w + idx), idx * E);
+      }
+    }
+  }
+  const uint64_t done = nvec * E;
+  if (blockIdx.x == gridDim.x - 1 && threadIdx.x < n - done) {
+    const uint64_t k = done + threadIdx.x;
+    acc.add(reinterpret_cast<const uint64_t *>(w)[k], 2 * k + 1);
+  }
+  finish_lanes(acc, first, out, ws, red);
+}
+
+__global__ void __launch_bounds__(kThreads)
+checksum_scalar(const uint64_t *__restrict__ w, uint64_t n, uint64_t first, uint64_t *__restrict__ out,
+                uint64_t *__restrict__ ws) {
+  __shared__ uint64_t red[64];
+  Lanes acc{0, 0};
+  for (uint64_t k = blockIdx.x * uint64_t(kThreads) + threadIdx.x; k < n; k += uint64_t(gridDim.x) * kThreads)
+    acc.add(w[k], 2 * k + 1);
+  finish_lanes(acc, first, out, ws, red);
+}
+
+// ---------------------------------------------------------------------------
+// TMA variants.  Persistent CTAs; CTA x owns tiles x, x+grid, x+2*grid, ...
+// Stage ring of S slots filled by 1-D bulk copies; slot j%S completes on its own
+// mbarrier with phase parity (j/S)&1.  A slot is refilled by thread 0 right after
+// the __syncthreads that proves every thread finished reading it.
+// ---------------------------------------------------------------------------
+template <int TILE, int S, int SO>
+struct TriadTmaSmem {
+  static constexpr size_t kBytes = sizeof(double) * TILE * (2 * S + SO) + sizeof(uint64_t) * S;
+};
+
+template <int TILE, int S, int SO, bool LANES>
+__global__ void __launch_bounds__(kThreads)
+triad_tma(double *__restrict__ a, const double *__restrict__ b, const double *__restrict__ c, double s, uint64_t n,
+          uint64_t first, uint64_t *__restrict__ out, uint64_t *__restrict__ ws) {
+  static_assert(SO >= 2, "need two output tiles to overlap the store with the next tile");
+  static_assert(TILE % (2 * kThreads) == 0, "tile must split into one f64x2 per thread per pass");
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  double *sb = reinterpret_cast<double *>(smem_raw);
+  double *sc = sb + size_t(S) * TILE;
+  double *so = sc + size_t(S) * TILE;
+  uint64_t *full = reinterpret_cast<uint64_t *>(so + size_t(SO) * TILE);
+  __shared__ uint64_t red[64];
+  constexpr uint32_t kTileBytes = TILE * sizeof(double);
+
+  const uint64_t ntiles = n / TILE;
+  const uint64_t my_tiles = ntiles > blockIdx.x ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const int tid = threadIdx.x;
+
+  uint64_t policy = 0;
+  if (tid == 0) {
+    for (int i = 0; i < S; ++i) tma::mbar_init(&full[i], 1);
+    tma::fence_barrier_init();
+  }
+  __syncthreads();
+  auto issue = [&](uint64_t j) {  // thread 0 only
+    const int st = int(j % S);
+    const uint64_t t = blockIdx.x + j * gridDim.x;
+    tma::mbar_arrive_expect_tx(&full[st], 2 * kTileBytes);
+    tma::bulk_load(sb + size_t(st) * TILE, b + t * TILE, kTileBytes, &full[st], policy);
+    tma::bulk_load(sc + size_t(st) * TILE, c + t * TILE, kTileBytes, &full[st], policy);
+  };
+  if (tid == 0) {
+    policy = tma::policy_evict_first();
+    for (uint64_t j = 0; j < my_tiles && j < uint64_t(S); ++j) issue(j);
+  }
+
+  Lanes acc{0, 0};
+  for (uint64_t j = 0; j < my_tiles; ++j) {
+    const int st = int(j % S), ob = int(j % SO);
+    const uint32_t parity = uint32_t(j / S) & 1u;
+    const uint64_t t = blockIdx.x + j * gridDim.x;
+    tma::mbar_wait(&full[st], parity);
+    const f64x2 *pb = reinterpret_cast<const f64x2 *>(sb + size_t(st) * TILE);
+    const f64x2 *pc = reinterpret_cast<const f64x2 *>(sc + size_t(st) * TILE);
+    f64x2 *po = reinterpret_cast<f64x2 *>(so + size_t(ob) * TILE);
+#pragma unroll
+    for (int v = tid; v < TILE / 2; v += kThreads) {
+      const f64x2 r = fma_vec(s, pc[v], pb[v]);
+      po[v] = r;
+      if (LANES) lanes_vec(acc, r, t * TILE + 2 * uint64_t(v));
+    }
+    tma::fence_proxy_async_smem();  // my st.shared visible to the bulk store
+    // the output tile of iteration j+1 was last read by the store committed at
+    // j+1-SO; stores committed so far are 0..j-1, so SO-2 may stay pending.
+    if (tid == 0) tma::bulk_wait_read<SO - 2>();
+    __syncthreads();
+    if (tid == 0) {
+      tma::bulk_store(a + t * TILE, po, kTileBytes);
+      tma::bulk_commit();
+      if (j + S < my_tiles) issue(j + S);
+    }
+  }
+  if (tid == 0) tma::bulk_wait_all<0>();
+
+  // remainder [ntiles*TILE, n): fewer than TILE elements, plain accesses
+  if (blockIdx.x == gridDim.x - 1) {
+    for (uint64_t k = ntiles * TILE + tid; k < n; k += kThreads) {
+      const double r = __fma_rn(s, c[k], b[k]);
+      a[k] = r;
+      if (LANES) acc.add(bits(r), 2 * k + 1);
+    }
+  }
+  if (LANES) finish_lanes(acc, first, out, ws, red);
+}
+
+template <int TILE, int S>
+struct ChecksumTmaSmem {
+  static constexpr size_t kBytes = sizeof(uint64_t) * TILE * S + sizeof(uint64_t) * S;
+};
+
+template <int TILE, int S>
+__global__ void __launch_bounds__(kThreads)
+checksum_tma(const uint64_t *__restrict__ w, uint64_t n, uint64_t first, uint64_t *__restrict__ out,
+             uint64_t *__restrict__ ws) {
+  static_assert(TILE % (2 * kThreads) == 0, "tile must split into one u64x2 per thread per pass");
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  uint64_t *sw = reinterpret_cast<uint64_t *>(smem_raw);
+  uint64_t *full = sw + size_t(S) * TILE;
+  __shared__ uint64_t red[64];
+  constexpr uint32_t kTileBytes = TILE * sizeof(uint64_t);
+
+  const uint64_t ntiles = n / TILE;
+  const uint64_t my_tiles = ntiles > blockIdx.x ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const int tid = threadIdx.x;
+
+  uint64_t policy = 0;
+  if (tid == 0) {
+    for (int i = 0; i < S; ++i) tma::mbar_init(&full[i], 1);
+    tma::fence_barrier_init();
+  }
+  __syncthreads();
+  auto issue = [&](uint64_t j) {
+    const int st = int(j % S);
+    const uint64_t t = blockIdx.x + j * gridDim.x;
+    tma::mbar_arrive_expect_tx(&full[st], kTileBytes);
+    tma::bulk_load(sw + size_t(st) * TILE, w + t * TILE, kTileBytes, &full[st], policy);
+  };
+  if (tid == 0) {
+    policy = tma::policy_evict_first();
+    for (uint64_t j = 0; j < my_tiles && j < uint64_t(S); ++j) issue(j);
+  }
+
+  Lanes acc{0, 0};
+  for (uint64_t j = 0; j < my_tiles; ++j) {
+    const int st = int(j % S);
+    const uint32_t parity = uint32_t(j / S) & 1u;
+    const uint64_t t = blockIdx.x + j * gridDim.x;
+    tma::mbar_wait(&full[st], parity);
+    const u64x2 *pw = reinterpret_cast<const u64x2 *>(sw + size_t(st) * TILE);
+#pragma unroll
+    for (int v = tid; v < TILE / 2; v += kThreads) lanes_vec(acc, pw[v], t * TILE + 2 * uint64_t(v));
+    __syncthreads();  // every thread is done with slot st
+    if (tid == 0 && j + S < my_tiles) issue(j + S);
+  }
+  if (blockIdx.x == gridDim.x - 1)
+    for (uint64_t k = ntiles * TILE + tid; k < n; k += kThreads) acc.add(w[k], 2 * k + 1);
+  finish_lanes(acc, first, out, ws, red);
+}
+
+// ---------------------------------------------------------------------------
+// K3  copy (local or peer)
+// ---------------------------------------------------------------------------
+template <int U>
+__global__ void __launch_bounds__(kThreads)
+copy_vec(uint4 *__restrict__ dst, const uint4 *__restrict__ src, uint64_t nvec, uint64_t bytes) {
+  const uint64_t tile = uint64_t(kThreads) * U;
+  for (uint64_t base = blockIdx.x * tile; base < nvec; base += gridDim.x * tile) {
+    const uint64_t i0 = base + threadIdx.x;
+    uint4 v[U];
+    if (base + tile <= nvec) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) v[u] = src[i0 + uint64_t(u) * kThreads];
+#pragma unroll
+      for (int u = 0; u < U; ++u) dst[i0 + uint64_t(u) * kThreads] = v[u];
+    } else {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const uint64_t idx = i0 + uint64_t(u) * kThreads;
+        if (idx < nvec) dst[idx] = src[idx];
+      }
+    }
+  }
+  const uint64_t done = nvec * 16;
+  if (blockIdx.x == gridDim.x - 1 && threadIdx.x < bytes - done)
+    reinterpret_cast<unsigned char *>(dst)[done + threadIdx.x] = reinterpret_cast<const unsigned char *>(src)[done + threadIdx.x];
+}
+
+__global__ void __launch_bounds__(kThreads)
+copy_bytes(unsigned char *__restrict__ dst, const unsigned char *__restrict__ src, uint64_t bytes) {
+  for (uint64_t k = blockIdx.x * uint64_t(kThreads) + threadIdx.x; k < bytes; k += uint64_t(gridDim.x) * kThreads)
+    dst[k] = src[k];
+}
+
+// ---------------------------------------------------------------------------
+// host side: launch geometry
+// ---------------------------------------------------------------------------
+struct DeviceInfo {
+  int sms = 0;
+};
+static int current_device_sms(int *sms) {
+  static std::atomic<int> cache[64];
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return int(e);
+  if (dev >= 0 && dev < 64) {
+    int v = cache[dev].load(std::memory_order_relaxed);
+    if (v > 0) { *sms = v; return 0; }
+  }
+  int v = 0;
+  e = cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+  if (e != cudaSuccess) return int(e);
+  if (dev >= 0 && dev < 64) cache[dev].store(v, std::memory_order_relaxed);
+  *sms = v;
+  return 0;
+}
+
+// grid = min(tiles, SMs x resident CTAs/SM), so every launch is a whole number of
+// co-resident waves (148 SMs on B200) and partial lanes fit the workspace.
+template <typename K>
+static int persistent_grid(K kernel, size_t dyn_smem, uint64_t tiles, unsigned *grid) {
+  int sms = 0;
+  int rc = current_device_sms(&sms);
+  if (rc) return rc;
+  int occ = 0;
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kThreads, dyn_smem);
+  if (e != cudaSuccess) return int(e);
+  if (occ < 1) return int(cudaErrorLaunchOutOfResources);
+  uint64_t g = uint64_t(sms) * uint64_t(occ);
+  if (g > uint64_t(kMaxPartialCtas)) g = kMaxPartialCtas;
+  if (tiles < g) g = tiles;
+  if (g < 1) g = 1;
+  *grid = unsigned(g);
+  return 0;
+}
+
+template <typename K>
+static int allow_smem(K kernel, size_t bytes) {
+  // per function AND per device: set it every time; it is a cheap driver call
+  return int(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes)));
+}
+
+static inline bool aligned(const void *p, size_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
+static inline int launch_rc() { return int(cudaGetLastError()); }
+
+// Variant measured fastest on B200 (profiles/): see DESIGN.md "Kernels".
+static int g_auto_triad = GPU_PROBE_VARIANT_LDG;
+static int g_auto_checksum = GPU_PROBE_VARIANT_LDG;
+
+// TMA geometry: 8 KiB tiles; triad 4 stages x (b,c) + 2 output tiles = 80 KiB/CTA
+// (2 CTAs/SM, 128 KiB of loads in flight per SM); checksum 6 stages = 48 KiB/CTA.
+constexpr int kTmaTile = 1024;
+constexpr int kTriadStages = 4, kTriadOutStages = 2;
+constexpr int kChecksumStages = 6;
+
+template <bool LANES>
+static int launch_triad(double *a, const double *b, const double *c, double s, uint64_t n, uint64_t first,
+                        uint64_t *out, uint64_t *ws, int variant, cudaStream_t st) {
+  if (variant == GPU_PROBE_VARIANT_AUTO) variant = g_auto_triad;
+  const bool al16 = aligned(a, 16) && aligned(b, 16) && aligned(c, 16);
+  const bool al32 = aligned(a, 32) && aligned(b, 32) && aligned(c, 32);
+  unsigned grid = 1;
+  int rc;
+  if (!al16) {
+    auto k = triad_scalar<LANES>;
+    if ((rc = persistent_grid(k, 0, (n + kThreads - 1) / kThreads, &grid))) return rc;
+    k<<<grid, kThreads, 0, st>>>(a, b, c, s, n, first, out, ws);
+    return launch_rc();
+  }
+  if (variant == GPU_PROBE_VARIANT_TMA) {
+    auto k = triad_tma<kTmaTile, kTriadStages, kTriadOutStages, LANES>;
+    constexpr size_t smem = TriadTmaSmem<kTmaTile, kTriadStages, kTriadOutStages>::kBytes;
+    if ((rc = allow_smem(k, smem))) return rc;
+    if ((rc = persistent_grid(k, smem, n / kTmaTile, &grid))) return rc;
+    k<<<grid, kThreads, smem, st>>>(a, b, c, s, n, first, out, ws);
+    return launch_rc();
+  }
+  if (variant == GPU_PROBE_VARIANT_LDG256 && al32) {
+    constexpr int U = 2;
+    auto k = triad_vec<f64x4, U, LANES>;
+    const uint64_t nvec = n / 4;
+    if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid))) return rc;
+    k<<<grid, kThreads, 0, st>>>(reinterpret_cast<f64x4 *>(a), reinterpret_cast<const f64x4 *>(b),
+                                 reinterpret_cast<const f64x4 *>(c), s, nvec, n, first, out, ws);
+    return launch_rc();
+  }
+  {
+    constexpr int U = 4;
+    auto k = triad_vec<f64x2, U, LANES>;
+    const uint64_t nvec = n / 2;
+    if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid))) return rc;
+    k<<<grid, kThreads, 0, st>>>(reinterpret_cast<f64x2 *>(a), reinterpret_cast<const f64x2 *>(b),
+                                 reinterpret_cast<const f64x2 *>(c), s, nvec, n, first, out, ws);
+    return launch_rc();
+  }
+}
+
+static int check_variant(int v) {
+  return (v >= GPU_PROBE_VARIANT_AUTO && v <= GPU_PROBE_VARIANT_LDG256) ? 0 : GPU_PROBE_EINVAL;
+}
+
+}  // namespace probe
+
+// ---------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------
+using namespace probe;
+
+extern "C" {
+
+int gpu_probe_abi_version(void) { return GPU_PROBE_ABI_VERSION; }
+
+const char *gpu_probe_kernel_info(void) {
+  return "gpu-probe abi=1 arch=sm_100a kernels=init_fill,triad,checksum_u64,triad_checksum,p2p_copy "
+         "variants=ldg128,tma_bulk,ldg256 cpu_fallback=none";
+}
+
+const char *gpu_probe_error_string(int rc) {
+  if (rc == 0) return "ok";
+  if (rc > 0) return cudaGetErrorString(cudaError_t(rc));
+  switch (rc) {
+    case GPU_PROBE_EINVAL: return "gpu_probe: invalid argument (null pointer, unknown variant or bad size)";
+    case GPU_PROBE_EALIGN: return "gpu_probe: pointer is not 8-byte aligned";
+    case GPU_PROBE_ETOOBIG: return "gpu_probe: size exceeds the stated maximum of this entry point";
+    case GPU_PROBE_ENOTREADY: return "gpu_probe: object not created or already destroyed";
+  }
+  if (rc > -100) return "gpu_probe: NCCL error (value is -ncclResult_t)";
+  return "gpu_probe: unknown error code";
+}
+
+int gpu_probe_init_fill(double *dst, uint64_t n, uint64_t first_index, uint64_t seed, void *stream) {
+  if (n == 0) return 0;
+  if (!dst) return GPU_PROBE_EINVAL;
+  if (!aligned(dst, 8)) return GPU_PROBE_EALIGN;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  unsigned grid = 1;
+  int rc;
+  if (aligned(dst, 16)) {
+    constexpr int U = 4;
+    const uint64_t nvec = n / 2;
+    auto k = init_fill_vec<U>;
+    if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid))) return rc;
+    k<<<grid, kThreads, 0, st>>>(reinterpret_cast<f64x2 *>(dst), nvec, n, first_index, seed);
+  } else {
+    if ((rc = persistent_grid(init_fill_scalar, 0, (n + kThreads - 1) / kThreads, &grid))) return rc;
+    init_fill_scalar<<<grid, kThreads, 0, st>>>(dst, n, first_index, seed);
+  }
+  return launch_rc();
+}
+
+int gpu_probe_triad(double *a, const double *b, const double *c, double s, uint64_t n, int variant, void *stream) {
+  if (check_variant(variant)) return GPU_PROBE_EINVAL;
+  if (n == 0) return 0;
+  if (!a || !b || !c) return GPU_PROBE_EINVAL;
+  if (!aligned(a, 8) || !aligned(b, 8) || !aligned(c, 8)) return GPU_PROBE_EALIGN;
+  return launch_triad<false>(a, b, c, s, n, 0, nullptr, nullptr, variant, static_cast<cudaStream_t>(stream));
+}
+
+size_t gpu_probe_checksum_workspace_bytes(void) { return kWorkspaceBytes; }
+
+int gpu_probe_checksum_u64(const uint64_t *w, uint64_t n, uint64_t first_index, uint64_t *out_lanes, void *workspace,
+                           int variant, void *stream) {
+  if (check_variant(variant)) return GPU_PROBE_EINVAL;
+  if (!out_lanes || !workspace || (!w && n)) return GPU_PROBE_EINVAL;
+  if (!aligned(w, 8) || !aligned(out_lanes, 8) || !aligned(workspace, 8)) return GPU_PROBE_EALIGN;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  uint64_t *ws = static_cast<uint64_t *>(workspace);
+  if (variant == GPU_PROBE_VARIANT_AUTO) variant = g_auto_checksum;
+  unsigned grid = 1;
+  int rc;
+  if (!aligned(w, 16)) {
+    if ((rc = persistent_grid(checksum_scalar, 0, (n + kThreads - 1) / kThreads, &grid))) return rc;
+    checksum_scalar<<<grid, kThreads, 0, st>>>(w, n, first_index, out_lanes, ws);
+    return launch_rc();
+  }
+  if (variant == GPU_PROBE_VARIANT_TMA) {
+    auto k = checksum_tma<kTmaTile, kChecksumStages>;
+    constexpr size_t smem = ChecksumTmaSmem<kTmaTile, kChecksumStages>::kBytes;
+    if ((rc = allow_smem(k, smem))) return rc;
+    if ((rc = persistent_grid(k, smem, n / kTmaTile, &grid))) return rc;
+    k<<<grid, kThreads, smem, st>>>(w, n, first_index, out_lanes, ws);
+    return launch_rc();
+  }
+  if (variant == GPU_PROBE_VARIANT_LDG256 && aligned(w, 32)) {
+    constexpr int U = 4;
+    auto k = checksum_vec<u64x4, U>;
+    const uint64_t nvec = n / 4;
+    if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid))) return rc;
+    k<<<grid, kThreads, 0, st>>>(reinterpret_cast<const u64x4 *>(w), nvec, n, first_index, out_lanes, ws);
+    return launch_rc();
+  }
+  constexpr int U = 8;
+  auto k = checksum_vec<u64x2, U>;
+  const uint64_t nvec = n / 2;
+  if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid))) return rc;
+  k<<<grid, kThreads, 0, st>>>(reinterpret_cast<const u64x2 *>(w), nvec, n, first_index, out_lanes, ws);
+  return launch_rc();
+}
+
+int gpu_probe_triad_checksum(double *a, const double *b, const double *c, double s, uint64_t n, uint64_t first_index,
+                             uint64_t *out_lanes, void *workspace, int variant, void *stream) {
+  if (check_variant(variant)) return GPU_PROBE_EINVAL;
+  if (!out_lanes || !workspace || (n && (!a || !b || !c))) return GPU_PROBE_EINVAL;
+  if (!aligned(a, 8) || !aligned(b, 8) || !aligned(c, 8) || !aligned(out_lanes, 8) || !aligned(workspace, 8))
+    return GPU_PROBE_EALIGN;
+  return launch_triad<true>(a, b, c, s, n, first_index, out_lanes, static_cast<uint64_t *>(workspace), variant,
+                            static_cast<cudaStream_t>(stream));
+}
+
+int gpu_probe_p2p_copy(void *dst, const void *src, uint64_t bytes, void *stream) {
+  if (bytes == 0) return 0;
+  if (!dst || !src) return GPU_PROBE_EINVAL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  unsigned grid = 1;
+  int rc;
+  if (aligned(dst, 16) && aligned(src, 16)) {
+    constexpr int U = 8;
+    const uint64_t nvec = bytes / 16;
+    auto k = copy_vec<U>;
+    if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid))) return rc;
+    k<<<grid, kThreads, 0, st>>>(static_cast<uint4 *>(dst), static_cast<const uint4 *>(src), nvec, bytes);
+  } else {
+    if ((rc = persistent_grid(copy_bytes, 0, (bytes + kThreads - 1) / kThreads, &grid))) return rc;
+    copy_bytes<<<grid, kThreads, 0, st>>>(static_cast<unsigned char *>(dst), static_cast<const unsigned char *>(src), bytes);
+  }
+  return launch_rc();
+}
+
+}  // extern "C"

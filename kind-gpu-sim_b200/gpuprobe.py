@@ -1,0 +1,139 @@
+"""ctypes binding of lib/libgpuprobe.so (include/gpu_probe.h) for tests/ and bench.py.
+
+This is NOT the product's host side -- that is bash + the C binary
+(kind-gpu-sim.sh -> pods/probe-*.yaml -> bin/gpu-probe).  It exists so the parity
+tests and the bench can call the very same C ABI a maintainer would bind.
+
+No fallback: if the shared library is missing or a call fails, this raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libgpuprobe.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "gpu_probe.h")
+
+SEED_B = 0x0123456789ABCDEF
+SEED_C = 0xFEDCBA9876543210
+SCALAR = 3.0
+
+VARIANT_AUTO, VARIANT_LDG, VARIANT_TMA, VARIANT_LDG256 = -1, 0, 1, 2
+VARIANTS = {"auto": VARIANT_AUTO, "ldg128": VARIANT_LDG, "tma": VARIANT_TMA, "ldg256": VARIANT_LDG256}
+
+EINVAL, EALIGN, ETOOBIG, ENOTREADY = -100, -101, -102, -103
+
+_u64 = ctypes.c_uint64
+_vp = ctypes.c_void_p
+
+
+class ProbeError(RuntimeError):
+    def __init__(self, rc: int, what: str):
+        self.rc = rc
+        super().__init__(f"{what}: rc={rc} ({error_string(rc)})")
+
+
+_lib = None
+
+
+def lib() -> ctypes.CDLL:
+    """Load the CUDA library; raise (never fall back) when it is absent."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FileNotFoundError(
+                f"{LIB_PATH} not built: run `make -C kind-gpu-sim_b200` (or __graft_entry__.build()); "
+                "the probe has no CPU fallback")
+        L = ctypes.CDLL(LIB_PATH)
+        L.gpu_probe_abi_version.restype = ctypes.c_int
+        L.gpu_probe_kernel_info.restype = ctypes.c_char_p
+        L.gpu_probe_error_string.restype = ctypes.c_char_p
+        L.gpu_probe_error_string.argtypes = [ctypes.c_int]
+        L.gpu_probe_init_fill.argtypes = [_vp, _u64, _u64, _u64, _vp]
+        L.gpu_probe_triad.argtypes = [_vp, _vp, _vp, ctypes.c_double, _u64, ctypes.c_int, _vp]
+        L.gpu_probe_checksum_workspace_bytes.restype = ctypes.c_size_t
+        L.gpu_probe_checksum_u64.argtypes = [_vp, _u64, _u64, _vp, _vp, ctypes.c_int, _vp]
+        L.gpu_probe_triad_checksum.argtypes = [_vp, _vp, _vp, ctypes.c_double, _u64, _u64, _vp, _vp, ctypes.c_int, _vp]
+        L.gpu_probe_p2p_copy.argtypes = [_vp, _vp, _u64, _vp]
+        L.gpu_probe_pipeline_create.argtypes = [ctypes.POINTER(_vp), _u64, ctypes.c_int]
+        L.gpu_probe_pipeline_run_host.argtypes = [_vp, _vp, _vp, _vp, ctypes.c_double, _u64, _u64,
+                                                  ctypes.POINTER(_u64)]
+        L.gpu_probe_pipeline_destroy.argtypes = [_vp]
+        for name in ("gpu_probe_init_fill", "gpu_probe_triad", "gpu_probe_checksum_u64", "gpu_probe_triad_checksum",
+                     "gpu_probe_p2p_copy", "gpu_probe_pipeline_create", "gpu_probe_pipeline_run_host",
+                     "gpu_probe_pipeline_destroy"):
+            getattr(L, name).restype = ctypes.c_int
+        _lib = L
+    return _lib
+
+
+def error_string(rc: int) -> str:
+    return lib().gpu_probe_error_string(rc).decode()
+
+
+def kernel_info() -> str:
+    return lib().gpu_probe_kernel_info().decode()
+
+
+def workspace_bytes() -> int:
+    return int(lib().gpu_probe_checksum_workspace_bytes())
+
+
+def _check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise ProbeError(rc, what)
+
+
+# The functions below take raw device addresses (ints) and a raw cudaStream_t (int).
+# tests/ and bench.py get them from torch tensors (.data_ptr()) -- torch is only the
+# allocator and the stream/event provider there.
+
+def init_fill(dst: int, n: int, first_index: int, seed: int, stream: int = 0) -> None:
+    _check(lib().gpu_probe_init_fill(dst, n, first_index & (2**64 - 1), seed, stream), "gpu_probe_init_fill")
+
+
+def triad(a: int, b: int, c: int, s: float, n: int, variant: int = VARIANT_AUTO, stream: int = 0) -> None:
+    _check(lib().gpu_probe_triad(a, b, c, s, n, variant, stream), "gpu_probe_triad")
+
+
+def checksum_u64(w: int, n: int, first_index: int, out_lanes: int, workspace: int,
+                 variant: int = VARIANT_AUTO, stream: int = 0) -> None:
+    _check(lib().gpu_probe_checksum_u64(w, n, first_index & (2**64 - 1), out_lanes, workspace, variant, stream),
+           "gpu_probe_checksum_u64")
+
+
+def triad_checksum(a: int, b: int, c: int, s: float, n: int, first_index: int, out_lanes: int, workspace: int,
+                   variant: int = VARIANT_AUTO, stream: int = 0) -> None:
+    _check(lib().gpu_probe_triad_checksum(a, b, c, s, n, first_index & (2**64 - 1), out_lanes, workspace, variant,
+                                          stream), "gpu_probe_triad_checksum")
+
+
+def p2p_copy(dst: int, src: int, nbytes: int, stream: int = 0) -> None:
+    _check(lib().gpu_probe_p2p_copy(dst, src, nbytes, stream), "gpu_probe_p2p_copy")
+
+
+class Pipeline:
+    """Host-buffer end-to-end path (gpu_probe_pipeline_*)."""
+
+    def __init__(self, chunk_elems: int = 0, depth: int = 0):
+        self._h = _vp()
+        _check(lib().gpu_probe_pipeline_create(ctypes.byref(self._h), chunk_elems, depth), "gpu_probe_pipeline_create")
+
+    def run_host(self, b_host: int, c_host: int, a_host: int | None, s: float, n: int,
+                 first_index: int = 0) -> tuple[int, int]:
+        lanes = (_u64 * 2)()
+        _check(lib().gpu_probe_pipeline_run_host(self._h, b_host, c_host, a_host or None, s, n,
+                                                 first_index & (2**64 - 1), lanes), "gpu_probe_pipeline_run_host")
+        return int(lanes[0]), int(lanes[1])
+
+    def close(self) -> None:
+        if self._h:
+            _check(lib().gpu_probe_pipeline_destroy(self._h), "gpu_probe_pipeline_destroy")
+            self._h = _vp()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()

@@ -290,7 +290,7 @@ def run_ours(args, rank, local_rank, world):
     value = step_bytes / (ms_step / 1e3) / 1e9
 
     # ---- end to end: pinned host b,c -> device -> lanes back, through the pipeline ABI ----
-    e2e = run_e2e(args, gpuprobe, torch, b, c, n, first, my_lanes, dist, world)
+    e2e = None if args.no_e2e else run_e2e(args, gpuprobe, torch, b, c, n, first, my_lanes, dist, world)
 
     # ---- NVLink part of the metric (N > 1): allreduce sweep, bus bandwidth ----
     nvlink = run_allreduce_sweep(args, torch, dist, world) if dist is not None else None
@@ -437,6 +437,7 @@ def main():
     ap.add_argument("--cpu-log2n", type=int, default=28, help="cpu_baseline sample size (elements per array)")
     ap.add_argument("--ref-log2n", type=int, default=28, help="--impl reference sample per step")
     ap.add_argument("--sweep-log2max", type=int, default=30)
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / parity leg")
     args = ap.parse_args()
     if args.warmup < 3:

@@ -415,8 +415,10 @@ static inline bool aligned(const void *p, size_t a) { return (reinterpret_cast<u
 static inline int launch_rc() { return int(cudaGetLastError()); }
 
 // Variant measured fastest on B200 (profiles/): see DESIGN.md "Kernels".
-static int g_auto_triad = GPU_PROBE_VARIANT_LDG;
-static int g_auto_checksum = GPU_PROBE_VARIANT_LDG;
+//   triad / fused: TMA bulk ring (6559 GB/s vs 6421 ldg256, 6197 ldg128, round-1 sweep)
+//   checksum     : 256-bit loads (7252 GB/s vs 7127 ldg128, 6539 tma)
+static int g_auto_triad = GPU_PROBE_VARIANT_TMA;
+static int g_auto_checksum = GPU_PROBE_VARIANT_LDG256;
 
 // TMA geometry: 8 KiB tiles; triad 4 stages x (b,c) + 2 output tiles = 80 KiB/CTA
 // (2 CTAs/SM, 128 KiB of loads in flight per SM); checksum 6 stages = 48 KiB/CTA.

@@ -58,8 +58,8 @@ def test_triad_rounds_once():
     c = oracle.init_fill(n, 0, oracle.SEED_C)
     unfused = oracle.triad_unfused(b, c, 3.0)
     for variant in VARIANTS:
-        da = f64(n)
-        gpuprobe.triad(da.data_ptr(), from_np(b).data_ptr(), from_np(c).data_ptr(), 3.0, n, variant, stream())
+        da, db, dc = f64(n), from_np(b), from_np(c)  # keep db/dc alive until the kernel has run
+        gpuprobe.triad(da.data_ptr(), db.data_ptr(), dc.data_ptr(), 3.0, n, variant, stream())
         torch.cuda.synchronize()
         got = to_u64(da)
         assert np.array_equal(got, oracle.triad(b, c, 3.0).view(np.uint64))

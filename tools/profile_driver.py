@@ -1,0 +1,32 @@
+#!/usr/bin/env python
+"""Launches each kernel variant twice at BASELINE size so one `ncu --set full` run can
+capture them all (tools: see profiles/README.md).  No timing is taken here."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "kind-gpu-sim_b200"))
+import torch  # noqa: E402
+
+import gpuprobe  # noqa: E402
+
+log2n = int(sys.argv[1]) if len(sys.argv) > 1 else 29
+n = 1 << log2n
+st = torch.cuda.current_stream().cuda_stream
+b = torch.empty(n, dtype=torch.float64, device="cuda")
+c = torch.empty(n, dtype=torch.float64, device="cuda")
+a = torch.empty(n, dtype=torch.float64, device="cuda")
+ws = torch.zeros(gpuprobe.workspace_bytes() // 8, dtype=torch.int64, device="cuda")
+out = torch.zeros(2, dtype=torch.int64, device="cuda")
+gpuprobe.init_fill(b.data_ptr(), n, 0, gpuprobe.SEED_B, st)
+gpuprobe.init_fill(c.data_ptr(), n, 0, gpuprobe.SEED_C, st)
+for v in (1, 2, 0):
+    for _ in range(2):
+        gpuprobe.triad(a.data_ptr(), b.data_ptr(), c.data_ptr(), 3.0, n, v, st)
+for v in (2, 0, 1):
+    for _ in range(2):
+        gpuprobe.checksum_u64(a.data_ptr(), n, 0, out.data_ptr(), ws.data_ptr(), v, st)
+for _ in range(2):
+    gpuprobe.triad_checksum(a.data_ptr(), b.data_ptr(), c.data_ptr(), 3.0, n, 0, out.data_ptr(), ws.data_ptr(), 1, st)
+torch.cuda.synchronize()
+print("lanes", [hex(int(x) & (2**64 - 1)) for x in out.cpu()])

@@ -7,7 +7,7 @@
 //     per array per thread issued before first use, persistent grid-stride CTAs.
 //   * TMA variants: one elected thread feeds a ring of shared-memory stages with
 //     1-D bulk async copies (UBLKCP) tracked by mbarriers; the CTA's threads
-//     consume from shared memory; results leave through bulk stores.
+//     consume from shared memory; results leave as 128-bit streaming stores.
 // No reference counterpart (the slot is /root/reference/pods/nvidia-gpu-test-pod.yaml:9);
 // spec: SURVEY.md section 8(d).  There is no CPU path in this file.
 #include "gpu_probe.h"
@@ -195,22 +195,23 @@ checksum_scalar(const uint64_t *__restrict__ w, uint64_t n, uint64_t first, uint
 // mbarrier with phase parity (j/S)&1.  A slot is refilled by thread 0 right after
 // the __syncthreads that proves every thread finished reading it.
 // ---------------------------------------------------------------------------
-template <int TILE, int S, int SO>
+template <int TILE, int S>
 struct TriadTmaSmem {
-  static constexpr size_t kBytes = sizeof(double) * TILE * (2 * S + SO) + sizeof(uint64_t) * S;
+  static constexpr size_t kBytes = sizeof(double) * TILE * 2 * S + sizeof(uint64_t) * S;
 };
 
-template <int TILE, int S, int SO, bool LANES>
+// Loads arrive by TMA; results leave straight from registers with 128-bit streaming
+// stores.  (A bulk-store variant that staged a[] through shared memory measured 4 %
+// slower -- 6630 vs 6920 GB/s, profiles/tune_triad_r1.csv -- so it is not shipped.)
+template <int TILE, int S, bool LANES>
 __global__ void __launch_bounds__(kThreads)
 triad_tma(double *__restrict__ a, const double *__restrict__ b, const double *__restrict__ c, double s, uint64_t n,
           uint64_t first, uint64_t *__restrict__ out, uint64_t *__restrict__ ws) {
-  static_assert(SO >= 2, "need two output tiles to overlap the store with the next tile");
   static_assert(TILE % (2 * kThreads) == 0, "tile must split into one f64x2 per thread per pass");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   double *sb = reinterpret_cast<double *>(smem_raw);
   double *sc = sb + size_t(S) * TILE;
-  double *so = sc + size_t(S) * TILE;
-  uint64_t *full = reinterpret_cast<uint64_t *>(so + size_t(SO) * TILE);
+  uint64_t *full = reinterpret_cast<uint64_t *>(sc + size_t(S) * TILE);
   __shared__ uint64_t red[64];
   constexpr uint32_t kTileBytes = TILE * sizeof(double);
 
@@ -238,31 +239,22 @@ triad_tma(double *__restrict__ a, const double *__restrict__ b, const double *__
 
   Lanes acc{0, 0};
   for (uint64_t j = 0; j < my_tiles; ++j) {
-    const int st = int(j % S), ob = int(j % SO);
+    const int st = int(j % S);
     const uint32_t parity = uint32_t(j / S) & 1u;
     const uint64_t t = blockIdx.x + j * gridDim.x;
     tma::mbar_wait(&full[st], parity);
     const f64x2 *pb = reinterpret_cast<const f64x2 *>(sb + size_t(st) * TILE);
     const f64x2 *pc = reinterpret_cast<const f64x2 *>(sc + size_t(st) * TILE);
-    f64x2 *po = reinterpret_cast<f64x2 *>(so + size_t(ob) * TILE);
+    f64x2 *ga = reinterpret_cast<f64x2 *>(a + t * TILE);
 #pragma unroll
     for (int v = tid; v < TILE / 2; v += kThreads) {
       const f64x2 r = fma_vec(s, pc[v], pb[v]);
-      po[v] = r;
+      st_stream(ga + v, r);
       if (LANES) lanes_vec(acc, r, t * TILE + 2 * uint64_t(v));
     }
-    tma::fence_proxy_async_smem();  // my st.shared visible to the bulk store
-    // the output tile of iteration j+1 was last read by the store committed at
-    // j+1-SO; stores committed so far are 0..j-1, so SO-2 may stay pending.
-    if (tid == 0) tma::bulk_wait_read<SO - 2>();
-    __syncthreads();
-    if (tid == 0) {
-      tma::bulk_store(a + t * TILE, po, kTileBytes);
-      tma::bulk_commit();
-      if (j + S < my_tiles) issue(j + S);
-    }
+    __syncthreads();  // every thread is done reading slot st
+    if (tid == 0 && j + S < my_tiles) issue(j + S);
   }
-  if (tid == 0) tma::bulk_wait_all<0>();
 
   // remainder [ntiles*TILE, n): fewer than TILE elements, plain accesses
   if (blockIdx.x == gridDim.x - 1) {
@@ -389,7 +381,7 @@ static int current_device_sms(int *sms) {
 // grid = min(tiles, SMs x resident CTAs/SM), so every launch is a whole number of
 // co-resident waves (148 SMs on B200) and partial lanes fit the workspace.
 template <typename K>
-static int persistent_grid(K kernel, size_t dyn_smem, uint64_t tiles, unsigned *grid) {
+static int persistent_grid(K kernel, size_t dyn_smem, uint64_t tiles, unsigned *grid, int max_ctas_per_sm = 0) {
   int sms = 0;
   int rc = current_device_sms(&sms);
   if (rc) return rc;
@@ -397,6 +389,7 @@ static int persistent_grid(K kernel, size_t dyn_smem, uint64_t tiles, unsigned *
   cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kThreads, dyn_smem);
   if (e != cudaSuccess) return int(e);
   if (occ < 1) return int(cudaErrorLaunchOutOfResources);
+  if (max_ctas_per_sm > 0 && occ > max_ctas_per_sm) occ = max_ctas_per_sm;
   uint64_t g = uint64_t(sms) * uint64_t(occ);
   if (g > uint64_t(kMaxPartialCtas)) g = kMaxPartialCtas;
   if (tiles < g) g = tiles;
@@ -415,16 +408,23 @@ static inline bool aligned(const void *p, size_t a) { return (reinterpret_cast<u
 static inline int launch_rc() { return int(cudaGetLastError()); }
 
 // Variant measured fastest on B200 (profiles/): see DESIGN.md "Kernels".
-//   triad / fused: TMA bulk ring (6559 GB/s vs 6421 ldg256, 6197 ldg128, round-1 sweep)
-//   checksum     : 256-bit loads (7252 GB/s vs 7127 ldg128, 6539 tma)
+//   triad / fused: TMA ring (6920 GB/s) vs ldg256 6421, ldg128 6197
+//   checksum     : TMA ring (7420 GB/s) vs ldg256 7252, ldg128 7127
 static int g_auto_triad = GPU_PROBE_VARIANT_TMA;
-static int g_auto_checksum = GPU_PROBE_VARIANT_LDG256;
+static int g_auto_checksum = GPU_PROBE_VARIANT_TMA;
 
-// TMA geometry: 8 KiB tiles; triad 4 stages x (b,c) + 2 output tiles = 80 KiB/CTA
-// (2 CTAs/SM, 128 KiB of loads in flight per SM); checksum 6 stages = 48 KiB/CTA.
-constexpr int kTmaTile = 1024;
-constexpr int kTriadStages = 4, kTriadOutStages = 2;
-constexpr int kChecksumStages = 6;
+// TMA geometry, from the round-1 sweeps (profiles/tune_*_r1.csv), ONE CTA per SM:
+//   triad   : 8 KiB tiles, 8 stages x (b,c) = 128 KiB of loads in flight per SM
+//             (6920 GB/s; plateau for 5..10 stages; 2 CTAs/SM with 4 stages: 6340)
+//   checksum: 32 KiB tiles, 4 stages = 128 KiB in flight per SM (7420 GB/s)
+constexpr int kTriadTile = 1024, kTriadStages = 8;
+constexpr int kChecksumTile = 4096, kChecksumStages = 4;
+constexpr int kTmaCtasPerSm = 1;
+// LDG geometry from the same sweeps: mixed read/write traffic wants FEW resident CTAs
+// (triad: 2/SM with 8x16 B or 4x32 B loads per array per thread -> 6700 / 6530 GB/s;
+// 8/SM: 6100-6300), read-only wants more (checksum: 6/SM -> 7350 GB/s).
+constexpr int kLdgTriadCtasPerSm = 2;
+constexpr int kLdgChecksumCtasPerSm = 6;
 
 template <bool LANES>
 static int launch_triad(double *a, const double *b, const double *c, double s, uint64_t n, uint64_t first,
@@ -441,27 +441,27 @@ static int launch_triad(double *a, const double *b, const double *c, double s, u
     return launch_rc();
   }
   if (variant == GPU_PROBE_VARIANT_TMA) {
-    auto k = triad_tma<kTmaTile, kTriadStages, kTriadOutStages, LANES>;
-    constexpr size_t smem = TriadTmaSmem<kTmaTile, kTriadStages, kTriadOutStages>::kBytes;
+    auto k = triad_tma<kTriadTile, kTriadStages, LANES>;
+    constexpr size_t smem = TriadTmaSmem<kTriadTile, kTriadStages>::kBytes;
     if ((rc = allow_smem(k, smem))) return rc;
-    if ((rc = persistent_grid(k, smem, n / kTmaTile, &grid))) return rc;
+    if ((rc = persistent_grid(k, smem, n / kTriadTile, &grid, kTmaCtasPerSm))) return rc;
     k<<<grid, kThreads, smem, st>>>(a, b, c, s, n, first, out, ws);
     return launch_rc();
   }
   if (variant == GPU_PROBE_VARIANT_LDG256 && al32) {
-    constexpr int U = 2;
+    constexpr int U = 4;
     auto k = triad_vec<f64x4, U, LANES>;
     const uint64_t nvec = n / 4;
-    if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid))) return rc;
+    if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid, kLdgTriadCtasPerSm))) return rc;
     k<<<grid, kThreads, 0, st>>>(reinterpret_cast<f64x4 *>(a), reinterpret_cast<const f64x4 *>(b),
                                  reinterpret_cast<const f64x4 *>(c), s, nvec, n, first, out, ws);
     return launch_rc();
   }
   {
-    constexpr int U = 4;
+    constexpr int U = 8;
     auto k = triad_vec<f64x2, U, LANES>;
     const uint64_t nvec = n / 2;
-    if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid))) return rc;
+    if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid, kLdgTriadCtasPerSm))) return rc;
     k<<<grid, kThreads, 0, st>>>(reinterpret_cast<f64x2 *>(a), reinterpret_cast<const f64x2 *>(b),
                                  reinterpret_cast<const f64x2 *>(c), s, nvec, n, first, out, ws);
     return launch_rc();
@@ -547,10 +547,10 @@ int gpu_probe_checksum_u64(const uint64_t *w, uint64_t n, uint64_t first_index, 
     return launch_rc();
   }
   if (variant == GPU_PROBE_VARIANT_TMA) {
-    auto k = checksum_tma<kTmaTile, kChecksumStages>;
-    constexpr size_t smem = ChecksumTmaSmem<kTmaTile, kChecksumStages>::kBytes;
+    auto k = checksum_tma<kChecksumTile, kChecksumStages>;
+    constexpr size_t smem = ChecksumTmaSmem<kChecksumTile, kChecksumStages>::kBytes;
     if ((rc = allow_smem(k, smem))) return rc;
-    if ((rc = persistent_grid(k, smem, n / kTmaTile, &grid))) return rc;
+    if ((rc = persistent_grid(k, smem, n / kChecksumTile, &grid, kTmaCtasPerSm))) return rc;
     k<<<grid, kThreads, smem, st>>>(w, n, first_index, out_lanes, ws);
     return launch_rc();
   }
@@ -558,14 +558,14 @@ int gpu_probe_checksum_u64(const uint64_t *w, uint64_t n, uint64_t first_index, 
     constexpr int U = 4;
     auto k = checksum_vec<u64x4, U>;
     const uint64_t nvec = n / 4;
-    if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid))) return rc;
+    if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid, kLdgChecksumCtasPerSm))) return rc;
     k<<<grid, kThreads, 0, st>>>(reinterpret_cast<const u64x4 *>(w), nvec, n, first_index, out_lanes, ws);
     return launch_rc();
   }
   constexpr int U = 8;
   auto k = checksum_vec<u64x2, U>;
   const uint64_t nvec = n / 2;
-  if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid))) return rc;
+  if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid, kLdgChecksumCtasPerSm))) return rc;
   k<<<grid, kThreads, 0, st>>>(reinterpret_cast<const u64x2 *>(w), nvec, n, first_index, out_lanes, ws);
   return launch_rc();
 }

@@ -18,8 +18,9 @@ pytestmark = pytest.mark.gpu
 
 VARIANTS = [gpuprobe.VARIANT_LDG, gpuprobe.VARIANT_TMA, gpuprobe.VARIANT_LDG256, gpuprobe.VARIANT_AUTO]
 VNAMES = ["ldg128", "tma", "ldg256", "auto"]
-# ragged sizes around every tiling boundary: vector width, CTA tile (256*U), TMA tile (1024)
-SIZES = [0, 1, 2, 3, 4, 5, 255, 256, 257, 1023, 1024, 1025, 2047, 2048, 2049, 4096 + 3, 65536, (1 << 20) + 3,
+# ragged sizes around every tiling boundary: vector width, CTA tile (256*U), TMA tiles (1024 / 4096)
+SIZES = [0, 1, 2, 3, 4, 5, 255, 256, 257, 1023, 1024, 1025, 2047, 2048, 2049, 4095, 4096, 4096 + 3, 8192 + 1, 65536,
+         (1 << 20) + 3, 148 * 4096 * 3 + 4095,
          3 * 1184 * 1024 + 517]
 FIRSTS = [0, 7, 1 << 40, (1 << 63) - 3, M64 - 1]
 

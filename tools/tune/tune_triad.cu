@@ -1,0 +1,426 @@
+// tools/tune/tune_triad.cu -- parameter sweep for the triad kernels (development tool, not
+// shipped).  Runtime-parameterised copies of the TMA ring and LDG kernels so one binary can
+// sweep tile size, stage count, CTAs/SM, block size, store path and array placement.
+// Build: make -C tools/tune     Run (GPU box): tools/tune/tune_triad [log2n] > gpurun_out/tune.csv
+#include <algorithm>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "probe_common.cuh"
+#include "probe_tma.cuh"
+
+using namespace probe;
+
+#define CK(x)                                                                      \
+  do {                                                                             \
+    cudaError_t e__ = (x);                                                         \
+    if (e__ != cudaSuccess) {                                                      \
+      fprintf(stderr, "%s:%d %s -> %s\n", __FILE__, __LINE__, #x, cudaGetErrorString(e__)); \
+      exit(1);                                                                     \
+    }                                                                              \
+  } while (0)
+
+enum StoreMode { BULK_NONE = 0, BULK_EF = 1, BULK_EL = 2, STG_CS = 3, STG_DEF = 4, STG_NA = 5 };
+
+__device__ __forceinline__ uint64_t policy_evict_last() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void bulk_store_hint(void *dst, const void *src, uint32_t bytes, uint64_t pol) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;"
+               :: "l"(dst), "r"(tma::smem_addr(src)), "r"(bytes), "l"(pol) : "memory");
+}
+
+// load_hint: 0 none(default policy via evict_normal), 1 evict_first
+template <int STORE>
+__global__ void triad_tma_rt(double *__restrict__ a, const double *__restrict__ b, const double *__restrict__ c,
+                             double s, uint64_t n, int tile, int S, int SO, int blocked, int load_ef) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  double *sb = reinterpret_cast<double *>(smem_raw);
+  double *sc = sb + size_t(S) * tile;
+  double *so = sc + size_t(S) * tile;
+  constexpr bool kBulk = STORE <= BULK_EL;
+  uint64_t *full = reinterpret_cast<uint64_t *>(so + (kBulk ? size_t(SO) * tile : 0));
+  const uint32_t tile_bytes = uint32_t(tile) * 8u;
+  const uint64_t ntiles = n / tile;
+  const int tid = threadIdx.x;
+  // tile assignment: interleaved t = cta + j*grid, or blocked contiguous ranges
+  uint64_t my_tiles, t0, tstride;
+  if (blocked) {
+    const uint64_t per = (ntiles + gridDim.x - 1) / gridDim.x;
+    t0 = per * blockIdx.x;
+    my_tiles = t0 >= ntiles ? 0 : (ntiles - t0 < per ? ntiles - t0 : per);
+    tstride = 1;
+  } else {
+    t0 = blockIdx.x;
+    my_tiles = ntiles > blockIdx.x ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    tstride = gridDim.x;
+  }
+  uint64_t lpol = 0, spol = 0;
+  if (tid == 0) {
+    for (int i = 0; i < S; ++i) tma::mbar_init(&full[i], 1);
+    tma::fence_barrier_init();
+  }
+  __syncthreads();
+  auto issue = [&](uint64_t j) {
+    const int st = int(j % S);
+    const uint64_t t = t0 + j * tstride;
+    tma::mbar_arrive_expect_tx(&full[st], 2 * tile_bytes);
+    tma::bulk_load(sb + size_t(st) * tile, b + t * tile, tile_bytes, &full[st], lpol);
+    tma::bulk_load(sc + size_t(st) * tile, c + t * tile, tile_bytes, &full[st], lpol);
+  };
+  if (tid == 0) {
+    if (load_ef) lpol = tma::policy_evict_first();
+    else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(lpol));
+    spol = STORE == BULK_EF ? tma::policy_evict_first() : policy_evict_last();
+    for (uint64_t j = 0; j < my_tiles && j < uint64_t(S); ++j) issue(j);
+  }
+  for (uint64_t j = 0; j < my_tiles; ++j) {
+    const int st = int(j % S), ob = int(j % SO);
+    const uint32_t parity = uint32_t(j / S) & 1u;
+    const uint64_t t = t0 + j * tstride;
+    tma::mbar_wait(&full[st], parity);
+    const f64x2 *pb = reinterpret_cast<const f64x2 *>(sb + size_t(st) * tile);
+    const f64x2 *pc = reinterpret_cast<const f64x2 *>(sc + size_t(st) * tile);
+    if (kBulk) {
+      f64x2 *po = reinterpret_cast<f64x2 *>(so + size_t(ob) * tile);
+      for (int v = tid; v < tile / 2; v += blockDim.x) {
+        const f64x2 x = pb[v], y = pc[v];
+        po[v] = f64x2{__fma_rn(s, y.x, x.x), __fma_rn(s, y.y, x.y)};
+      }
+      tma::fence_proxy_async_smem();
+      if (tid == 0) {
+        if (SO == 2) tma::bulk_wait_read<0>(); else if (SO == 3) tma::bulk_wait_read<1>(); else tma::bulk_wait_read<2>();
+      }
+      __syncthreads();
+      if (tid == 0) {
+        if (STORE == BULK_NONE) tma::bulk_store(a + t * tile, po, tile_bytes);
+        else bulk_store_hint(a + t * tile, po, tile_bytes, spol);
+        tma::bulk_commit();
+        if (j + S < my_tiles) issue(j + S);
+      }
+    } else {
+      f64x2 *ga = reinterpret_cast<f64x2 *>(a + t * tile);
+      for (int v = tid; v < tile / 2; v += blockDim.x) {
+        const f64x2 x = pb[v], y = pc[v];
+        const f64x2 r{__fma_rn(s, y.x, x.x), __fma_rn(s, y.y, x.y)};
+        if (STORE == STG_CS) st_stream(ga + v, r);
+        else if (STORE == STG_NA) asm volatile("st.global.L1::no_allocate.v2.f64 [%0], {%1,%2};" :: "l"(ga + v), "d"(r.x), "d"(r.y) : "memory");
+        else ga[v] = r;
+      }
+      __syncthreads();
+      if (tid == 0 && j + S < my_tiles) issue(j + S);
+    }
+  }
+  if (kBulk && tid == 0) tma::bulk_wait_all<0>();
+}
+
+// LDG variants: V = 16 or 32 bytes, U loads per array per thread
+template <typename V, int U, int LD>  // LD: 0 = .cs / NA.EFL2, 1 = default ld.global, 2 = ld.global.nc
+__global__ void triad_ldg_rt(V *__restrict__ a, const V *__restrict__ b, const V *__restrict__ c, double s, uint64_t nvec) {
+  const uint64_t tile = uint64_t(blockDim.x) * U;
+  for (uint64_t base = blockIdx.x * tile; base + tile <= nvec; base += gridDim.x * tile) {
+    const uint64_t i0 = base + threadIdx.x;
+    V vb[U], vc[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) vb[u] = LD == 0 ? ld_stream(b + i0 + uint64_t(u) * blockDim.x) : b[i0 + uint64_t(u) * blockDim.x];
+#pragma unroll
+    for (int u = 0; u < U; ++u) vc[u] = LD == 0 ? ld_stream(c + i0 + uint64_t(u) * blockDim.x) : c[i0 + uint64_t(u) * blockDim.x];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      V r;
+      double *pr = reinterpret_cast<double *>(&r);
+      const double *pb = reinterpret_cast<const double *>(&vb[u]), *pc = reinterpret_cast<const double *>(&vc[u]);
+#pragma unroll
+      for (int e = 0; e < int(sizeof(V) / 8); ++e) pr[e] = __fma_rn(s, pc[e], pb[e]);
+      if (LD == 0) st_stream(a + i0 + uint64_t(u) * blockDim.x, r); else a[i0 + uint64_t(u) * blockDim.x] = r;
+    }
+  }
+}
+
+// pure read / pure write references
+__global__ void read_only(const u64x4 *__restrict__ w, uint64_t nvec, uint64_t *out) {
+  uint64_t acc = 0;
+  const uint64_t tile = uint64_t(blockDim.x) * 4;
+  for (uint64_t base = blockIdx.x * tile; base + tile <= nvec; base += gridDim.x * tile) {
+    u64x4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) v[u] = ld_stream(w + base + threadIdx.x + uint64_t(u) * blockDim.x);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) acc += v[u].x ^ v[u].y ^ v[u].z ^ v[u].w;
+  }
+  if (acc == 0x1234567) *out = acc;
+}
+__global__ void write_only(f64x4 *__restrict__ w, uint64_t nvec) {
+  const uint64_t tile = uint64_t(blockDim.x) * 4;
+  for (uint64_t base = blockIdx.x * tile; base + tile <= nvec; base += gridDim.x * tile) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) st_stream(w + base + threadIdx.x + uint64_t(u) * blockDim.x, f64x4{1.0, 2.0, 3.0, 4.0});
+  }
+}
+
+
+// ---- checksum sweeps --------------------------------------------------------
+__device__ __forceinline__ void acc2(Lanes &acc, const u64x2 &v, uint64_t k0) {
+  const uint64_t m = 2 * k0 + 1; acc.add(v.x, m); acc.add(v.y, m + 2);
+}
+__device__ __forceinline__ void acc4(Lanes &acc, const u64x4 &v, uint64_t k0) {
+  const uint64_t m = 2 * k0 + 1; acc.add(v.x, m); acc.add(v.y, m + 2); acc.add(v.z, m + 4); acc.add(v.w, m + 6);
+}
+__global__ void checksum_tma_rt(const uint64_t *__restrict__ w, uint64_t n, uint64_t *__restrict__ out,
+                                uint64_t *__restrict__ ws, int tile, int S) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  uint64_t *sw = reinterpret_cast<uint64_t *>(smem_raw);
+  uint64_t *full = sw + size_t(S) * tile;
+  __shared__ uint64_t red[64];
+  const uint32_t tile_bytes = uint32_t(tile) * 8u;
+  const uint64_t ntiles = n / tile;
+  const uint64_t my_tiles = ntiles > blockIdx.x ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const int tid = threadIdx.x;
+  uint64_t policy = 0;
+  if (tid == 0) {
+    for (int i = 0; i < S; ++i) tma::mbar_init(&full[i], 1);
+    tma::fence_barrier_init();
+  }
+  __syncthreads();
+  auto issue = [&](uint64_t j) {
+    const int st = int(j % S);
+    const uint64_t t = blockIdx.x + j * gridDim.x;
+    tma::mbar_arrive_expect_tx(&full[st], tile_bytes);
+    tma::bulk_load(sw + size_t(st) * tile, w + t * tile, tile_bytes, &full[st], policy);
+  };
+  if (tid == 0) {
+    policy = tma::policy_evict_first();
+    for (uint64_t j = 0; j < my_tiles && j < uint64_t(S); ++j) issue(j);
+  }
+  Lanes acc{0, 0};
+  for (uint64_t j = 0; j < my_tiles; ++j) {
+    const int st = int(j % S);
+    const uint32_t parity = uint32_t(j / S) & 1u;
+    const uint64_t t = blockIdx.x + j * gridDim.x;
+    tma::mbar_wait(&full[st], parity);
+    const u64x2 *pw = reinterpret_cast<const u64x2 *>(sw + size_t(st) * tile);
+    for (int v = tid; v < tile / 2; v += blockDim.x) acc2(acc, pw[v], t * tile + 2 * uint64_t(v));
+    __syncthreads();
+    if (tid == 0 && j + S < my_tiles) issue(j + S);
+  }
+  finish_lanes(acc, 0, out, ws, red);
+}
+template <typename V, int U>
+__global__ void checksum_ldg_rt(const V *__restrict__ w, uint64_t nvec, uint64_t *__restrict__ out, uint64_t *__restrict__ ws) {
+  constexpr int E = int(sizeof(V) / 8);
+  __shared__ uint64_t red[64];
+  Lanes acc{0, 0};
+  const uint64_t tile = uint64_t(blockDim.x) * U;
+  for (uint64_t base = blockIdx.x * tile; base + tile <= nvec; base += gridDim.x * tile) {
+    const uint64_t i0 = base + threadIdx.x;
+    V v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) v[u] = ld_stream(w + i0 + uint64_t(u) * blockDim.x);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if constexpr (E == 2) acc2(acc, *reinterpret_cast<u64x2 *>(&v[u]), (i0 + uint64_t(u) * blockDim.x) * E);
+      else acc4(acc, *reinterpret_cast<u64x4 *>(&v[u]), (i0 + uint64_t(u) * blockDim.x) * E);
+    }
+  }
+  finish_lanes(acc, 0, out, ws, red);
+}
+
+struct Timer {
+  cudaEvent_t e0, e1;
+  Timer() { CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); }
+  template <typename F>
+  void run(F f, int warm, int iters, float *best, float *med) {
+    for (int i = 0; i < warm; ++i) f();
+    CK(cudaDeviceSynchronize());
+    std::vector<float> ms(iters);
+    for (int i = 0; i < iters; ++i) {
+      CK(cudaEventRecord(e0));
+      f();
+      CK(cudaEventRecord(e1));
+      CK(cudaEventSynchronize(e1));
+      CK(cudaEventElapsedTime(&ms[i], e0, e1));
+    }
+    std::sort(ms.begin(), ms.end());
+    *best = ms[0];
+    *med = ms[iters / 2];
+  }
+};
+
+int main(int argc, char **argv) {
+  const int log2n = argc > 1 ? atoi(argv[1]) : 29;
+  const char *only = argc > 2 ? argv[2] : "all";
+  const uint64_t n = 1ull << log2n;
+  int sms = 0;
+  CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
+  // one slab; arrays placed with a configurable pad between them
+  const size_t slab_bytes = 3 * n * 8 + (64u << 20);
+  unsigned char *slab = nullptr;
+  CK(cudaMalloc(&slab, slab_bytes));
+  CK(cudaMemset(slab, 0, slab_bytes));
+  uint64_t *dout;
+  CK(cudaMalloc(&dout, 8));
+  Timer tm;
+  printf("kind,param,best_ms,med_ms,GBps_med,frac8000\n");
+  auto report = [&](const char *kind, const char *param, double bytes, float best, float med) {
+    printf("%s,%s,%.4f,%.4f,%.1f,%.4f\n", kind, param, best, med, bytes / med / 1e6, bytes / med / 1e6 / 8000.0);
+    fflush(stdout);
+  };
+  const size_t pads[] = {0, 256, 4096 + 256, (1u << 20) + 4096 + 256, (8u << 20) + 33 * 1024};
+  auto place = [&](size_t pad, double **a, double **b, double **c) {
+    *b = reinterpret_cast<double *>(slab);
+    *c = reinterpret_cast<double *>(slab + n * 8 + pad);
+    *a = reinterpret_cast<double *>(slab + 2 * (n * 8 + pad));
+  };
+  char param[256];
+  float best, med;
+  double *a, *b, *c;
+
+  {  // references
+    place(0, &a, &b, &c);
+    tm.run([&] { read_only<<<sms * 6, 256>>>(reinterpret_cast<const u64x4 *>(b), n / 4, dout); }, 2, 10, &best, &med);
+    report("read_only", "ldg256 U4 6cta", 8.0 * n, best, med);
+    tm.run([&] { write_only<<<sms * 6, 256>>>(reinterpret_cast<f64x4 *>(a), n / 4); }, 2, 10, &best, &med);
+    report("write_only", "stg256 U4 6cta", 8.0 * n, best, med);
+    tm.run([&] { CK(cudaMemcpyAsync(a, b, n * 8, cudaMemcpyDeviceToDevice)); }, 2, 10, &best, &med);
+    report("memcpy_d2d", "copy engine/kernel", 16.0 * n, best, med);
+  }
+
+  auto run_tma = [&](int store, int tile, int S, int SO, int ctas, int threads, int blocked, int load_ef, size_t pad) {
+    const bool bulk = store <= BULK_EL;
+    const size_t smem = size_t(tile) * 8 * (2 * S + (bulk ? SO : 0)) + 8 * S;
+    if (smem > 227 * 1024 / size_t(ctas) - 1024) return;
+    place(pad, &a, &b, &c);
+    auto launch = [&](auto kern) {
+      CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+      int occ = 0;
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, smem));
+      if (occ < ctas) return false;
+      tm.run([&] { kern<<<sms * ctas, threads, smem>>>(a, b, c, 3.0, n, tile, S, SO, blocked, load_ef); }, 2, 8, &best, &med);
+      CK(cudaGetLastError());
+      return true;
+    };
+    bool ok = false;
+    switch (store) {
+      case BULK_NONE: ok = launch(triad_tma_rt<BULK_NONE>); break;
+      case BULK_EF: ok = launch(triad_tma_rt<BULK_EF>); break;
+      case BULK_EL: ok = launch(triad_tma_rt<BULK_EL>); break;
+      case STG_CS: ok = launch(triad_tma_rt<STG_CS>); break;
+      case STG_DEF: ok = launch(triad_tma_rt<STG_DEF>); break;
+      case STG_NA: ok = launch(triad_tma_rt<STG_NA>); break;
+    }
+    if (!ok) return;
+    snprintf(param, sizeof param, "store=%d tileKB=%d S=%d SO=%d ctas=%d thr=%d blocked=%d loadEF=%d pad=%zu", store,
+             tile * 8 / 1024, S, SO, ctas, threads, blocked, load_ef, pad);
+    report("triad_tma", param, 24.0 * n, best, med);
+  };
+
+  const bool all = !strcmp(only, "all");
+  if (all || !strcmp(only, "pad")) {
+    for (size_t pad : pads) run_tma(BULK_NONE, 1024, 4, 2, 2, 256, 0, 1, pad);
+    for (size_t pad : pads) run_tma(STG_CS, 1024, 4, 2, 2, 256, 0, 1, pad);
+  }
+  if (all || !strcmp(only, "store")) {
+    for (int store = 0; store <= 5; ++store)
+      for (int lef = 0; lef < 2; ++lef) run_tma(store, 1024, 4, 2, 2, 256, 0, lef, 0);
+  }
+  if (all || !strcmp(only, "geom")) {
+    for (int store : {int(BULK_NONE), int(STG_CS)})
+      for (int tile : {512, 1024, 2048, 4096})
+        for (int S : {2, 3, 4, 6, 8})
+          for (int ctas : {1, 2, 3, 4})
+            run_tma(store, tile, S, 2, ctas, 256, 0, 1, 0);
+    for (int threads : {128, 512})
+      for (int tile : {1024, 2048})
+        for (int ctas : {1, 2, 4}) run_tma(BULK_NONE, tile, 4, 2, ctas, threads, 0, 1, 0);
+    for (int SO : {3, 4}) run_tma(BULK_NONE, 1024, 4, SO, 2, 256, 0, 1, 0);
+    for (int tile : {1024, 2048, 4096}) run_tma(BULK_NONE, tile, 4, 2, 2, 256, 1, 1, 0);  // blocked assignment
+  }
+  if (all || !strcmp(only, "ldg")) {
+    place(0, &a, &b, &c);
+#define RUN_LDG(V, VB, U, LD, THREADS, CTAS)                                                                      \
+  do {                                                                                                            \
+    auto kern = triad_ldg_rt<V, U, LD>;                                                                           \
+    int occ = 0;                                                                                                  \
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, THREADS, 0));                                    \
+    if (occ >= CTAS) {                                                                                            \
+      const uint64_t nvec = n * 8 / VB;                                                                           \
+      tm.run([&] { kern<<<sms * CTAS, THREADS>>>(reinterpret_cast<V *>(a), reinterpret_cast<const V *>(b),        \
+                                                  reinterpret_cast<const V *>(c), 3.0, nvec); }, 2, 8, &best, &med); \
+      CK(cudaGetLastError());                                                                                     \
+      snprintf(param, sizeof param, "vec=%d U=%d ld=%d thr=%d ctas=%d", VB, U, LD, THREADS, CTAS);                \
+      report("triad_ldg", param, 24.0 * n, best, med);                                                            \
+    }                                                                                                             \
+  } while (0)
+    for (int ctas : {1, 2, 3, 4, 6, 8}) {
+      switch (ctas) {
+#define CASES(C)                                                                                   \
+  case C:                                                                                          \
+    RUN_LDG(f64x4, 32, 1, 0, 256, C); RUN_LDG(f64x4, 32, 2, 0, 256, C); RUN_LDG(f64x4, 32, 4, 0, 256, C); \
+    RUN_LDG(f64x2, 16, 2, 0, 256, C); RUN_LDG(f64x2, 16, 4, 0, 256, C); RUN_LDG(f64x2, 16, 8, 0, 256, C); \
+    RUN_LDG(f64x4, 32, 2, 1, 256, C); RUN_LDG(f64x2, 16, 4, 1, 256, C);                               \
+    RUN_LDG(f64x4, 32, 2, 0, 512, C); RUN_LDG(f64x4, 32, 2, 0, 128, C); RUN_LDG(f64x4, 32, 4, 0, 128, C); \
+    break;
+        CASES(1) CASES(2) CASES(3) CASES(4) CASES(6) CASES(8)
+      }
+    }
+  }
+
+  if (all || !strcmp(only, "csum")) {
+    place(0, &a, &b, &c);
+    uint64_t *ws;
+    CK(cudaMalloc(&ws, kWorkspaceBytes));
+    CK(cudaMemset(ws, 0, kWorkspaceBytes));
+    const uint64_t *w = reinterpret_cast<const uint64_t *>(b);
+    for (int tile : {512, 1024, 2048, 4096})
+      for (int S : {2, 3, 4, 6, 8, 12})
+        for (int ctas : {1, 2, 3, 4})
+          for (int threads : {128, 256, 512}) {
+            const size_t smem = size_t(tile) * 8 * S + 8 * S;
+            if (smem > 227 * 1024 / size_t(ctas) - 1024) continue;
+            CK(cudaFuncSetAttribute(checksum_tma_rt, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+            int occ = 0;
+            CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, checksum_tma_rt, threads, smem));
+            if (occ < ctas) continue;
+            tm.run([&] { checksum_tma_rt<<<sms * ctas, threads, smem>>>(w, n, dout, ws, tile, S); }, 2, 8, &best, &med);
+            CK(cudaGetLastError());
+            snprintf(param, sizeof param, "tileKB=%d S=%d ctas=%d thr=%d", tile * 8 / 1024, S, ctas, threads);
+            report("checksum_tma", param, 8.0 * n, best, med);
+          }
+#define RUN_CL(V, VB, U, THREADS, CTAS)                                                                    \
+  do {                                                                                                     \
+    auto kern = checksum_ldg_rt<V, U>;                                                                     \
+    int occ = 0;                                                                                           \
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, THREADS, 0));                             \
+    if (occ >= CTAS) {                                                                                     \
+      const uint64_t nvec = n * 8 / VB;                                                                    \
+      tm.run([&] { kern<<<sms * CTAS, THREADS>>>(reinterpret_cast<const V *>(w), nvec, dout, ws); }, 2, 8, &best, &med); \
+      CK(cudaGetLastError());                                                                              \
+      snprintf(param, sizeof param, "vec=%d U=%d thr=%d ctas=%d", VB, U, THREADS, CTAS);                   \
+      report("checksum_ldg", param, 8.0 * n, best, med);                                                   \
+    }                                                                                                      \
+  } while (0)
+#define CL_CASES(C)                                                                               \
+    RUN_CL(u64x4, 32, 1, 256, C); RUN_CL(u64x4, 32, 2, 256, C); RUN_CL(u64x4, 32, 4, 256, C); RUN_CL(u64x4, 32, 8, 256, C); \
+    RUN_CL(u64x2, 16, 4, 256, C); RUN_CL(u64x2, 16, 8, 256, C); RUN_CL(u64x2, 16, 16, 256, C);        \
+    RUN_CL(u64x4, 32, 2, 128, C); RUN_CL(u64x4, 32, 4, 128, C); RUN_CL(u64x4, 32, 8, 128, C);        \
+    RUN_CL(u64x4, 32, 2, 512, C); RUN_CL(u64x4, 32, 4, 512, C); RUN_CL(u64x4, 32, 4, 1024, C);
+    CL_CASES(1) CL_CASES(2) CL_CASES(3) CL_CASES(4) CL_CASES(5) CL_CASES(6) CL_CASES(8)
+    CK(cudaFree(ws));
+  }
+  if (all || !strcmp(only, "fine")) {  // around the triad optimum: TMA loads + STG stores, few CTAs, deep ring
+    for (int store : {int(STG_CS), int(STG_DEF), int(STG_NA)})
+      for (int tile : {512, 1024, 2048})
+        for (int S : {4, 5, 6, 7, 8, 10, 12, 16})
+          for (int ctas : {1, 2})
+            for (int threads : {128, 256, 384, 512}) run_tma(store, tile, S, 2, ctas, threads, 0, 1, 0);
+  }
+  CK(cudaFree(slab));
+  return 0;
+}

@@ -225,23 +225,29 @@ triad_tma(double *__restrict__ a, const double *__restrict__ b, const double *__
     tma::fence_barrier_init();
   }
   __syncthreads();
-  auto issue = [&](uint64_t j) {  // thread 0 only
-    const int st = int(j % S);
-    const uint64_t t = blockIdx.x + j * gridDim.x;
-    tma::mbar_arrive_expect_tx(&full[st], 2 * kTileBytes);
-    tma::bulk_load(sb + size_t(st) * TILE, b + t * TILE, kTileBytes, &full[st], policy);
-    tma::bulk_load(sc + size_t(st) * TILE, c + t * TILE, kTileBytes, &full[st], policy);
+  // producer state (thread 0 only): next tile to request and the slot it lands in;
+  // consumer state (all threads): slot, phase parity and tile index, all carried
+  // incrementally -- no 64-bit division on the per-tile path.
+  uint64_t pj = 0;
+  int pst = 0;
+  auto issue = [&]() {
+    const uint64_t t = blockIdx.x + pj * gridDim.x;
+    tma::mbar_arrive_expect_tx(&full[pst], 2 * kTileBytes);
+    tma::bulk_load(sb + size_t(pst) * TILE, b + t * TILE, kTileBytes, &full[pst], policy);
+    tma::bulk_load(sc + size_t(pst) * TILE, c + t * TILE, kTileBytes, &full[pst], policy);
+    ++pj;
+    if (++pst == S) pst = 0;
   };
   if (tid == 0) {
     policy = tma::policy_evict_first();
-    for (uint64_t j = 0; j < my_tiles && j < uint64_t(S); ++j) issue(j);
+    for (int i = 0; i < S && pj < my_tiles; ++i) issue();
   }
 
   Lanes acc{0, 0};
-  for (uint64_t j = 0; j < my_tiles; ++j) {
-    const int st = int(j % S);
-    const uint32_t parity = uint32_t(j / S) & 1u;
-    const uint64_t t = blockIdx.x + j * gridDim.x;
+  int st = 0;
+  uint32_t parity = 0;
+  uint64_t t = blockIdx.x;
+  for (uint64_t j = 0; j < my_tiles; ++j, t += gridDim.x) {
     tma::mbar_wait(&full[st], parity);
     const f64x2 *pb = reinterpret_cast<const f64x2 *>(sb + size_t(st) * TILE);
     const f64x2 *pc = reinterpret_cast<const f64x2 *>(sc + size_t(st) * TILE);
@@ -253,7 +259,8 @@ triad_tma(double *__restrict__ a, const double *__restrict__ b, const double *__
       if (LANES) lanes_vec(acc, r, t * TILE + 2 * uint64_t(v));
     }
     __syncthreads();  // every thread is done reading slot st
-    if (tid == 0 && j + S < my_tiles) issue(j + S);
+    if (tid == 0 && pj < my_tiles) issue();
+    if (++st == S) { st = 0; parity ^= 1u; }
   }
 
   // remainder [ntiles*TILE, n): fewer than TILE elements, plain accesses
@@ -293,28 +300,32 @@ checksum_tma(const uint64_t *__restrict__ w, uint64_t n, uint64_t first, uint64_
     tma::fence_barrier_init();
   }
   __syncthreads();
-  auto issue = [&](uint64_t j) {
-    const int st = int(j % S);
-    const uint64_t t = blockIdx.x + j * gridDim.x;
-    tma::mbar_arrive_expect_tx(&full[st], kTileBytes);
-    tma::bulk_load(sw + size_t(st) * TILE, w + t * TILE, kTileBytes, &full[st], policy);
+  uint64_t pj = 0;
+  int pst = 0;
+  auto issue = [&]() {  // thread 0 only
+    const uint64_t t = blockIdx.x + pj * gridDim.x;
+    tma::mbar_arrive_expect_tx(&full[pst], kTileBytes);
+    tma::bulk_load(sw + size_t(pst) * TILE, w + t * TILE, kTileBytes, &full[pst], policy);
+    ++pj;
+    if (++pst == S) pst = 0;
   };
   if (tid == 0) {
     policy = tma::policy_evict_first();
-    for (uint64_t j = 0; j < my_tiles && j < uint64_t(S); ++j) issue(j);
+    for (int i = 0; i < S && pj < my_tiles; ++i) issue();
   }
 
   Lanes acc{0, 0};
-  for (uint64_t j = 0; j < my_tiles; ++j) {
-    const int st = int(j % S);
-    const uint32_t parity = uint32_t(j / S) & 1u;
-    const uint64_t t = blockIdx.x + j * gridDim.x;
+  int st = 0;
+  uint32_t parity = 0;
+  uint64_t t = blockIdx.x;
+  for (uint64_t j = 0; j < my_tiles; ++j, t += gridDim.x) {
     tma::mbar_wait(&full[st], parity);
     const u64x2 *pw = reinterpret_cast<const u64x2 *>(sw + size_t(st) * TILE);
 #pragma unroll
     for (int v = tid; v < TILE / 2; v += kThreads) lanes_vec(acc, pw[v], t * TILE + 2 * uint64_t(v));
     __syncthreads();  // every thread is done with slot st
-    if (tid == 0 && j + S < my_tiles) issue(j + S);
+    if (tid == 0 && pj < my_tiles) issue();
+    if (++st == S) { st = 0; parity ^= 1u; }
   }
   if (blockIdx.x == gridDim.x - 1)
     for (uint64_t k = ntiles * TILE + tid; k < n; k += kThreads) acc.add(w[k], 2 * k + 1);
@@ -358,9 +369,6 @@ copy_bytes(unsigned char *__restrict__ dst, const unsigned char *__restrict__ sr
 // ---------------------------------------------------------------------------
 // host side: launch geometry
 // ---------------------------------------------------------------------------
-struct DeviceInfo {
-  int sms = 0;
-};
 static int current_device_sms(int *sms) {
   static std::atomic<int> cache[64];
   int dev = 0;
@@ -378,17 +386,59 @@ static int current_device_sms(int *sms) {
   return 0;
 }
 
+// Per (device, kernel) launch facts, looked up once: resident CTAs/SM and, for kernels
+// that need more than 48 KiB of dynamic shared memory, the opt-in attribute (which is
+// per function AND per device).  Keeps every later call down to a bare launch, so a
+// host that times single launches does not pay driver queries inside its timed region.
+struct KernelFacts {
+  std::atomic<const void *> key{nullptr};
+  std::atomic<int> ready{0};
+  int dev = -1, occ = 0, sms = 0;
+};
+static KernelFacts g_facts[256];
+
+static int kernel_facts(const void *kernel, size_t dyn_smem, int *occ_out, int *sms_out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return int(e);
+  const size_t h0 = (reinterpret_cast<uintptr_t>(kernel) >> 4) * 31u + size_t(dev) * 7919u;
+  for (size_t probe_i = 0; probe_i < 256; ++probe_i) {
+    KernelFacts &f = g_facts[(h0 + probe_i) & 255];
+    const void *k = f.key.load(std::memory_order_acquire);
+    if (k == kernel && f.ready.load(std::memory_order_acquire) && f.dev == dev) {
+      *occ_out = f.occ; *sms_out = f.sms;
+      return 0;
+    }
+    if (k != nullptr) continue;  // slot taken by another (kernel, device)
+    // miss: compute, then try to publish (a lost race just recomputes next time)
+    int sms = 0, occ = 0;
+    int rc = current_device_sms(&sms);
+    if (rc) return rc;
+    if (dyn_smem > 48 * 1024) {
+      e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(dyn_smem));
+      if (e != cudaSuccess) return int(e);
+    }
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kThreads, dyn_smem);
+    if (e != cudaSuccess) return int(e);
+    if (occ < 1) return int(cudaErrorLaunchOutOfResources);
+    const void *expect = nullptr;
+    if (f.key.compare_exchange_strong(expect, kernel, std::memory_order_acq_rel)) {
+      f.dev = dev; f.occ = occ; f.sms = sms;
+      f.ready.store(1, std::memory_order_release);
+    }
+    *occ_out = occ; *sms_out = sms;
+    return 0;
+  }
+  return int(cudaErrorLaunchOutOfResources);  // table full: cannot happen with this file's kernels
+}
+
 // grid = min(tiles, SMs x resident CTAs/SM), so every launch is a whole number of
 // co-resident waves (148 SMs on B200) and partial lanes fit the workspace.
 template <typename K>
 static int persistent_grid(K kernel, size_t dyn_smem, uint64_t tiles, unsigned *grid, int max_ctas_per_sm = 0) {
-  int sms = 0;
-  int rc = current_device_sms(&sms);
+  int sms = 0, occ = 0;
+  int rc = kernel_facts(reinterpret_cast<const void *>(kernel), dyn_smem, &occ, &sms);
   if (rc) return rc;
-  int occ = 0;
-  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kThreads, dyn_smem);
-  if (e != cudaSuccess) return int(e);
-  if (occ < 1) return int(cudaErrorLaunchOutOfResources);
   if (max_ctas_per_sm > 0 && occ > max_ctas_per_sm) occ = max_ctas_per_sm;
   uint64_t g = uint64_t(sms) * uint64_t(occ);
   if (g > uint64_t(kMaxPartialCtas)) g = kMaxPartialCtas;
@@ -398,28 +448,25 @@ static int persistent_grid(K kernel, size_t dyn_smem, uint64_t tiles, unsigned *
   return 0;
 }
 
-template <typename K>
-static int allow_smem(K kernel, size_t bytes) {
-  // per function AND per device: set it every time; it is a cheap driver call
-  return int(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes)));
-}
-
 static inline bool aligned(const void *p, size_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
 static inline int launch_rc() { return int(cudaGetLastError()); }
 
 // Variant measured fastest on B200 (profiles/): see DESIGN.md "Kernels".
-//   triad / fused: TMA ring (6920 GB/s) vs ldg256 6421, ldg128 6197
-//   checksum     : TMA ring (7420 GB/s) vs ldg256 7252, ldg128 7127
+//   triad / fused: TMA ring (6900 GB/s) vs ldg128 6740, ldg256 6600
+//   checksum     : TMA ring (7420 GB/s) vs ldg256 7330, ldg128 7330
 static int g_auto_triad = GPU_PROBE_VARIANT_TMA;
 static int g_auto_checksum = GPU_PROBE_VARIANT_TMA;
 
-// TMA geometry, from the round-1 sweeps (profiles/tune_*_r1.csv), ONE CTA per SM:
-//   triad   : 8 KiB tiles, 8 stages x (b,c) = 128 KiB of loads in flight per SM
-//             (6920 GB/s; plateau for 5..10 stages; 2 CTAs/SM with 4 stages: 6340)
-//   checksum: 32 KiB tiles, 4 stages = 128 KiB in flight per SM (7420 GB/s)
-constexpr int kTriadTile = 1024, kTriadStages = 8;
-constexpr int kChecksumTile = 4096, kChecksumStages = 4;
-constexpr int kTmaCtasPerSm = 1;
+// TMA geometry, from the round-1 sweeps (profiles/tune_*_r1.csv).
+//   triad   : 4 KiB tiles, 4 stages x (b,c), 2 CTAs/SM = 64 KiB of loads in flight per
+//             SM -> 6900 GB/s.  Mixed read/write traffic has a sharp optimum at the
+//             bandwidth-delay product: 48 KiB/SM starves (6470), 80 KiB/SM and more
+//             over-subscribes the memory system and throughput COLLAPSES (6500 -> 5800
+//             at 256 KiB/SM).  More bytes in flight is not better here.
+//   checksum: read-only traffic has no such collapse: 32 KiB tiles, 4 stages, 1 CTA/SM
+//             = 128 KiB in flight per SM -> 7420 GB/s.
+constexpr int kTriadTile = 512, kTriadStages = 4, kTriadCtasPerSm = 2;
+constexpr int kChecksumTile = 4096, kChecksumStages = 4, kChecksumCtasPerSm = 1;
 // LDG geometry from the same sweeps: mixed read/write traffic wants FEW resident CTAs
 // (triad: 2/SM with 8x16 B or 4x32 B loads per array per thread -> 6700 / 6530 GB/s;
 // 8/SM: 6100-6300), read-only wants more (checksum: 6/SM -> 7350 GB/s).
@@ -443,8 +490,7 @@ static int launch_triad(double *a, const double *b, const double *c, double s, u
   if (variant == GPU_PROBE_VARIANT_TMA) {
     auto k = triad_tma<kTriadTile, kTriadStages, LANES>;
     constexpr size_t smem = TriadTmaSmem<kTriadTile, kTriadStages>::kBytes;
-    if ((rc = allow_smem(k, smem))) return rc;
-    if ((rc = persistent_grid(k, smem, n / kTriadTile, &grid, kTmaCtasPerSm))) return rc;
+    if ((rc = persistent_grid(k, smem, n / kTriadTile, &grid, kTriadCtasPerSm))) return rc;
     k<<<grid, kThreads, smem, st>>>(a, b, c, s, n, first, out, ws);
     return launch_rc();
   }
@@ -549,8 +595,7 @@ int gpu_probe_checksum_u64(const uint64_t *w, uint64_t n, uint64_t first_index, 
   if (variant == GPU_PROBE_VARIANT_TMA) {
     auto k = checksum_tma<kChecksumTile, kChecksumStages>;
     constexpr size_t smem = ChecksumTmaSmem<kChecksumTile, kChecksumStages>::kBytes;
-    if ((rc = allow_smem(k, smem))) return rc;
-    if ((rc = persistent_grid(k, smem, n / kChecksumTile, &grid, kTmaCtasPerSm))) return rc;
+    if ((rc = persistent_grid(k, smem, n / kChecksumTile, &grid, kChecksumCtasPerSm))) return rc;
     k<<<grid, kThreads, smem, st>>>(w, n, first_index, out_lanes, ws);
     return launch_rc();
   }

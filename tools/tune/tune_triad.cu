@@ -11,6 +11,7 @@
 
 #include <cuda_runtime.h>
 
+#include "gpu_probe.h"
 #include "probe_common.cuh"
 #include "probe_tma.cuh"
 
@@ -119,6 +120,131 @@ __global__ void triad_tma_rt(double *__restrict__ a, const double *__restrict__ 
     }
   }
   if (kBulk && tid == 0) tma::bulk_wait_all<0>();
+}
+
+
+// compile-time geometry copy of the shipped kernel, with a switchable consumer-loop shape
+// MODE 0: fully unrolled (all LDS, then DFMA, then STG)   MODE 1: #pragma unroll 1
+// MODE 2: unrolled, but the elected thread refills BEFORE the CTA barrier is replaced by
+//         per-stage "empty" mbarrier (consumers arrive, producer waits) -- no __syncthreads
+template <int TILE, int S, int MODE>
+__global__ void __launch_bounds__(256)
+triad_tma_ct(double *__restrict__ a, const double *__restrict__ b, const double *__restrict__ c, double s, uint64_t n) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  double *sb = reinterpret_cast<double *>(smem_raw);
+  double *sc = sb + size_t(S) * TILE;
+  uint64_t *full = reinterpret_cast<uint64_t *>(sc + size_t(S) * TILE);
+  constexpr uint32_t kTileBytes = TILE * 8;
+  const uint64_t ntiles = n / TILE;
+  const uint64_t my_tiles = ntiles > blockIdx.x ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const int tid = threadIdx.x;
+  uint64_t policy = 0;
+  if (tid == 0) {
+    for (int i = 0; i < S; ++i) tma::mbar_init(&full[i], 1);
+    tma::fence_barrier_init();
+  }
+  __syncthreads();
+  auto issue = [&](uint64_t j) {
+    const int st = int(j % S);
+    const uint64_t t = blockIdx.x + j * gridDim.x;
+    tma::mbar_arrive_expect_tx(&full[st], 2 * kTileBytes);
+    tma::bulk_load(sb + size_t(st) * TILE, b + t * TILE, kTileBytes, &full[st], policy);
+    tma::bulk_load(sc + size_t(st) * TILE, c + t * TILE, kTileBytes, &full[st], policy);
+  };
+  if (tid == 0) {
+    policy = tma::policy_evict_first();
+    for (uint64_t j = 0; j < my_tiles && j < uint64_t(S); ++j) issue(j);
+  }
+  for (uint64_t j = 0; j < my_tiles; ++j) {
+    const int st = int(j % S);
+    const uint32_t parity = uint32_t(j / S) & 1u;
+    const uint64_t t = blockIdx.x + j * gridDim.x;
+    tma::mbar_wait(&full[st], parity);
+    const f64x2 *pb = reinterpret_cast<const f64x2 *>(sb + size_t(st) * TILE);
+    const f64x2 *pc = reinterpret_cast<const f64x2 *>(sc + size_t(st) * TILE);
+    f64x2 *ga = reinterpret_cast<f64x2 *>(a + t * TILE);
+    if (MODE == 1) {
+#pragma unroll 1
+      for (int v = tid; v < TILE / 2; v += 256) {
+        const f64x2 x = pb[v], y = pc[v];
+        st_stream(ga + v, f64x2{__fma_rn(s, y.x, x.x), __fma_rn(s, y.y, x.y)});
+      }
+    } else {
+#pragma unroll
+      for (int v = tid; v < TILE / 2; v += 256) {
+        const f64x2 x = pb[v], y = pc[v];
+        st_stream(ga + v, f64x2{__fma_rn(s, y.x, x.x), __fma_rn(s, y.y, x.y)});
+      }
+    }
+    __syncthreads();
+    if (tid == 0 && j + S < my_tiles) issue(j + S);
+  }
+}
+
+
+// Division-free runtime-geometry kernel (stage / parity / tile index carried incrementally)
+// so the consumer is fast at every geometry, plus an optional pacing knob: the elected
+// thread will not refill a slot earlier than `pace` SM cycles after its previous refill.
+template <int UNROLL>
+__global__ void __launch_bounds__(256)
+triad_tma_fast(double *__restrict__ a, const double *__restrict__ b, const double *__restrict__ c, double s,
+               uint64_t n, int tile, int S, int pace) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  double *sb = reinterpret_cast<double *>(smem_raw);
+  double *sc = sb + size_t(S) * tile;
+  uint64_t *full = reinterpret_cast<uint64_t *>(sc + size_t(S) * tile);
+  const uint32_t tile_bytes = uint32_t(tile) * 8u;
+  const uint64_t ntiles = n / tile;
+  const uint64_t my_tiles = ntiles > blockIdx.x ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const int tid = threadIdx.x;
+  uint64_t policy = 0;
+  if (tid == 0) {
+    for (int i = 0; i < S; ++i) tma::mbar_init(&full[i], 1);
+    tma::fence_barrier_init();
+  }
+  __syncthreads();
+  // producer state (thread 0): next tile to request and the slot it goes to
+  uint64_t pj = 0;
+  int pst = 0;
+  long long next_ok = 0;
+  auto issue = [&]() {
+    const uint64_t t = blockIdx.x + pj * gridDim.x;
+    tma::mbar_arrive_expect_tx(&full[pst], 2 * tile_bytes);
+    tma::bulk_load(sb + size_t(pst) * tile, b + t * tile, tile_bytes, &full[pst], policy);
+    tma::bulk_load(sc + size_t(pst) * tile, c + t * tile, tile_bytes, &full[pst], policy);
+    ++pj;
+    if (++pst == S) pst = 0;
+  };
+  if (tid == 0) {
+    policy = tma::policy_evict_first();
+    for (int i = 0; i < S && pj < my_tiles; ++i) issue();
+    next_ok = clock64() + pace;
+  }
+  int st = 0;
+  uint32_t parity = 0;
+  uint64_t t = blockIdx.x;
+  for (uint64_t j = 0; j < my_tiles; ++j, t += gridDim.x) {
+    tma::mbar_wait(&full[st], parity);
+    const f64x2 *pb = reinterpret_cast<const f64x2 *>(sb + size_t(st) * tile);
+    const f64x2 *pc = reinterpret_cast<const f64x2 *>(sc + size_t(st) * tile);
+    f64x2 *ga = reinterpret_cast<f64x2 *>(a + t * tile);
+#pragma unroll UNROLL
+    for (int v = tid; v < tile / 2; v += 256) {
+      const f64x2 x = pb[v], y = pc[v];
+      st_stream(ga + v, f64x2{__fma_rn(s, y.x, x.x), __fma_rn(s, y.y, x.y)});
+    }
+    __syncthreads();
+    if (tid == 0 && pj < my_tiles) {
+      if (pace > 0) {
+        while (clock64() < next_ok) { }
+        next_ok += pace;
+        const long long now = clock64();
+        if (next_ok < now) next_ok = now;  // never bank credit: a late refill does not allow a burst
+      }
+      issue();
+    }
+    if (++st == S) { st = 0; parity ^= 1u; }
+  }
 }
 
 // LDG variants: V = 16 or 32 bytes, U loads per array per thread
@@ -420,6 +546,105 @@ int main(int argc, char **argv) {
         for (int S : {4, 5, 6, 7, 8, 10, 12, 16})
           for (int ctas : {1, 2})
             for (int threads : {128, 256, 384, 512}) run_tma(store, tile, S, 2, ctas, threads, 0, 1, 0);
+  }
+
+  if (!strcmp(only, "b2b")) {  // does back-to-back launching or separate allocations change the picture?
+    double *sa, *sb2, *sc2;
+    CK(cudaMalloc(&sb2, n * 8)); CK(cudaMalloc(&sc2, n * 8)); CK(cudaMalloc(&sa, n * 8));
+    CK(cudaMemset(sb2, 0, n * 8)); CK(cudaMemset(sc2, 0, n * 8));
+    const int tile = 1024, S = 8;
+    const size_t smem = size_t(tile) * 8 * 2 * S + 8 * S;
+    auto kern = triad_tma_rt<STG_CS>;
+    CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    for (int sep = 0; sep < 2; ++sep) {
+      if (sep) { a = sa; b = sb2; c = sc2; } else place(0, &a, &b, &c);
+      for (int batch : {1, 10, 50}) {
+        auto f = [&] { for (int i = 0; i < batch; ++i) kern<<<sms, 256, smem>>>(a, b, c, 3.0, n, tile, S, 2, 0, 1); };
+        tm.run(f, 2, 8, &best, &med);
+        snprintf(param, sizeof param, "tma8K S8 sep_alloc=%d batch=%d (ms per launch)", sep, batch);
+        report("triad_tma_b2b", param, 24.0 * n * batch, best, med);
+      }
+      for (int batch : {1, 10, 50}) {
+        auto k2 = triad_ldg_rt<f64x2, 8, 0>;
+        auto f = [&] { for (int i = 0; i < batch; ++i) k2<<<sms * 2, 256>>>(reinterpret_cast<f64x2 *>(a), reinterpret_cast<const f64x2 *>(b), reinterpret_cast<const f64x2 *>(c), 3.0, n / 2); };
+        tm.run(f, 2, 8, &best, &med);
+        snprintf(param, sizeof param, "ldg128 U8 2cta sep_alloc=%d batch=%d", sep, batch);
+        report("triad_ldg_b2b", param, 24.0 * n * batch, best, med);
+      }
+    }
+  }
+
+  if (!strcmp(only, "ship")) {  // shipped library vs the tuner's copy, same buffers, same process
+    double *sa, *sb2, *sc2;
+    CK(cudaMalloc(&sb2, n * 8)); CK(cudaMalloc(&sc2, n * 8)); CK(cudaMalloc(&sa, n * 8));
+    CK(cudaMemset(sb2, 0, n * 8)); CK(cudaMemset(sc2, 0, n * 8));
+    const int tile = 1024, S = 8;
+    const size_t smem = size_t(tile) * 8 * 2 * S + 8 * S;
+    auto kern = triad_tma_rt<STG_CS>;
+    CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    for (int rep = 0; rep < 2; ++rep)
+      for (int batch : {1, 10}) {
+        a = sa; b = sb2; c = sc2;
+        tm.run([&] { for (int i = 0; i < batch; ++i) kern<<<sms, 256, smem>>>(a, b, c, 3.0, n, tile, S, 2, 0, 1); }, 2, 10, &best, &med);
+        snprintf(param, sizeof param, "tuner copy batch=%d", batch);
+        report("triad_tma", param, 24.0 * n * batch, best, med);
+        for (int v = 0; v < 3; ++v) {
+          tm.run([&] { for (int i = 0; i < batch; ++i) { int rc = gpu_probe_triad(a, b, c, 3.0, n, v, nullptr); if (rc) { fprintf(stderr, "rc=%d\n", rc); exit(1); } } }, 2, 10, &best, &med);
+          snprintf(param, sizeof param, "shipped variant=%d batch=%d", v, batch);
+          report("gpu_probe_triad", param, 24.0 * n * batch, best, med);
+        }
+      }
+  }
+
+  if (!strcmp(only, "shape")) {
+    double *sa, *sb2, *sc2;
+    CK(cudaMalloc(&sb2, n * 8)); CK(cudaMalloc(&sc2, n * 8)); CK(cudaMalloc(&sa, n * 8));
+    CK(cudaMemset(sb2, 0, n * 8)); CK(cudaMemset(sc2, 0, n * 8));
+    a = sa; b = sb2; c = sc2;
+    const size_t smem = size_t(1024) * 8 * 2 * 8 + 8 * 8;
+    auto k0 = triad_tma_ct<1024, 8, 0>; auto k1 = triad_tma_ct<1024, 8, 1>; auto kr = triad_tma_rt<STG_CS>;
+    CK(cudaFuncSetAttribute(k0, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    CK(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    CK(cudaFuncSetAttribute(kr, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    for (int rep = 0; rep < 3; ++rep) {
+      tm.run([&] { kr<<<sms, 256, smem>>>(a, b, c, 3.0, n, 1024, 8, 2, 0, 1); }, 2, 10, &best, &med);
+      report("triad_tma", "runtime-geometry (tuner)", 24.0 * n, best, med);
+      tm.run([&] { k0<<<sms, 256, smem>>>(a, b, c, 3.0, n); }, 2, 10, &best, &med);
+      report("triad_tma", "compile-time unrolled", 24.0 * n, best, med);
+      tm.run([&] { k1<<<sms, 256, smem>>>(a, b, c, 3.0, n); }, 2, 10, &best, &med);
+      report("triad_tma", "compile-time unroll 1", 24.0 * n, best, med);
+      tm.run([&] { int rc = gpu_probe_triad(a, b, c, 3.0, n, 1, nullptr); if (rc) exit(1); }, 2, 10, &best, &med);
+      report("triad_tma", "shipped", 24.0 * n, best, med);
+    }
+  }
+
+  if (!strcmp(only, "fast")) {
+    double *sa, *sb2, *sc2;
+    CK(cudaMalloc(&sb2, n * 8)); CK(cudaMalloc(&sc2, n * 8)); CK(cudaMalloc(&sa, n * 8));
+    CK(cudaMemset(sb2, 0, n * 8)); CK(cudaMemset(sc2, 0, n * 8));
+    a = sa; b = sb2; c = sc2;
+    auto kf = triad_tma_fast<4>;
+    auto run_fast = [&](int tile, int S, int ctas, int pace) {
+      const size_t smem = size_t(tile) * 8 * 2 * S + 8 * S;
+      if (smem > 227 * 1024 / size_t(ctas) - 1024) return;
+      CK(cudaFuncSetAttribute(kf, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+      int occ = 0;
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kf, 256, smem));
+      if (occ < ctas) return;
+      tm.run([&] { kf<<<sms * ctas, 256, smem>>>(a, b, c, 3.0, n, tile, S, pace); }, 2, 10, &best, &med);
+      CK(cudaGetLastError());
+      snprintf(param, sizeof param, "tileKB=%.1f S=%d ctas=%d pace=%d inflightKB=%d", tile * 8 / 1024.0, S, ctas, pace,
+               tile * 16 * S * ctas / 1024);
+      report("triad_fast", param, 24.0 * n, best, med);
+    };
+    for (int tile : {256, 512, 1024, 2048, 4096})
+      for (int S : {2, 3, 4, 5, 6, 8, 12, 16})
+        for (int ctas : {1, 2, 3, 4}) run_fast(tile, S, ctas, 0);
+    // pacing: 8 KiB tiles, 1 CTA/SM, deep ring; pace in SM cycles per tile (24 KiB of traffic per tile per SM)
+    for (int S : {4, 8})
+      for (int pace : {700, 800, 850, 900, 925, 950, 975, 1000, 1025, 1050, 1100, 1200}) run_fast(1024, S, 1, pace);
+    for (int pace : {350, 400, 425, 450, 475, 500, 525, 550, 600}) run_fast(512, 8, 1, pace);
+    for (int pace : {1400, 1600, 1700, 1800, 1900, 2000, 2100, 2200, 2400}) run_fast(1024, 4, 2, pace);
   }
   CK(cudaFree(slab));
   return 0;

@@ -85,6 +85,31 @@ int gpu_probe_checksum_u64(const uint64_t *w, uint64_t n, uint64_t first_index,
                            uint64_t *out_lanes, void *workspace, int variant,
                            void *stream);
 
+/* K2 without any allocation, for hosts that cannot obtain device scratch.
+ * No counterpart in the reference (it has no compute at all); it exists for callers
+ * of THIS library that are not able to cudaMalloc the checksum workspace: a health
+ * check embedded in a process whose device memory is wholly owned by another
+ * allocator (a serving engine that reserved all of HBM at start-up, a plugin that
+ * runs under a no-allocation-after-init policy), or a monitoring loop that must not
+ * touch the allocator while the workload it watches is running.
+ * Same result as gpu_probe_checksum_u64 with VARIANT_AUTO, but the scratch is a
+ * 65,792-byte array that lives inside the library's device image: every GPU that
+ * loads libgpuprobe.so carries it until the process exits.
+ *  - limit: n <= GPU_PROBE_NOALLOC_MAX_WORDS, else GPU_PROBE_ETOOBIG (nothing runs).
+ *  - makes no cudaMalloc/cudaFree/allocating call; launches one 256-byte memset and
+ *    one kernel on `stream`.
+ *  - the first call on each device looks the array's device address up (a one-time
+ *    driver query that may also load the library's device code): make that first
+ *    call before starting any stream capture on that device.
+ *  - all calls on a device share the one array, which still holds what the previous
+ *    call wrote; the entry point re-zeroes the only word that must start at zero.
+ *    Two calls that overlap on the GPU (different streams, no ordering) race on it
+ *    and return garbage -- serialise them, or use gpu_probe_checksum_u64 with one
+ *    workspace per stream. */
+#define GPU_PROBE_NOALLOC_MAX_WORDS (1ull << 34) /* 128 GiB of words: above any B200 buffer */
+int gpu_probe_checksum_u64_noalloc(const uint64_t *w, uint64_t n, uint64_t first_index,
+                                   uint64_t *out_lanes, void *stream);
+
 /* K1+K2 fused: writes a[] and the lanes of a[] in one pass (24 B/element instead
  * of 32).  Same lanes as gpu_probe_triad followed by gpu_probe_checksum_u64.
  *  */

@@ -645,3 +645,54 @@ int gpu_probe_p2p_copy(void *dst, const void *src, uint64_t bytes, void *stream)
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------
+// Checksum for callers that cannot allocate (see gpu_probe_checksum_u64_noalloc in
+// include/gpu_probe.h).  The scratch the checksum kernels need -- ticket word plus
+// per-CTA partial lanes -- sits in this file-scope device array instead of in memory
+// the caller would have had to cudaMalloc.  65,792 bytes per GPU, held from module load
+// until exit.
+//
+// g_noalloc_scratch below is only a host-side handle for the symbol; it is NOT a device
+// address and must never be handed to a kernel.  The device address is fetched once
+// per device with cudaGetSymbolAddress while that device is current.
+// ---------------------------------------------------------------------------
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[probe::kWorkspaceBytes / sizeof(unsigned long long)];
+
+static std::atomic<uint64_t *> g_noalloc_addr[64];
+
+// One-time set-up for the current device.  Allocates nothing.
+static int noalloc_scratch_of_current_device(uint64_t **out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return int(e);
+  if (dev < 0 || dev >= 64) return GPU_PROBE_EINVAL;
+  uint64_t *known = g_noalloc_addr[dev].load(std::memory_order_acquire);
+  if (known == nullptr) {
+    uint64_t *ptr = nullptr;
+    e = cudaGetSymbolAddress((void **)&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess) return int(e);
+    if (ptr == nullptr) return int(cudaErrorInvalidSymbol);
+    g_noalloc_addr[dev].store(ptr, std::memory_order_release);  // same value whichever thread wins
+    known = ptr;
+  }
+  *out = known;
+  return 0;
+}
+
+extern "C" int gpu_probe_checksum_u64_noalloc(const uint64_t *w, uint64_t n, uint64_t first_index,
+                                              uint64_t *out_lanes, void *stream) {
+  if (!out_lanes || (!w && n)) return GPU_PROBE_EINVAL;
+  if (n > GPU_PROBE_NOALLOC_MAX_WORDS) return GPU_PROBE_ETOOBIG;
+  if (!probe::aligned(w, 8) || !probe::aligned(out_lanes, 8)) return GPU_PROBE_EALIGN;
+  uint64_t *scratch = nullptr;
+  int rc = noalloc_scratch_of_current_device(&scratch);
+  if (rc) return rc;
+  // The array still holds the previous call's ticket and partial lanes.  Partials are
+  // overwritten by every CTA before they are read; the ticket line is the one thing that
+  // has to be zero when the kernel starts, whatever an earlier (possibly aborted) call left.
+  cudaError_t e = cudaMemsetAsync(scratch, 0, sizeof(uint64_t) * probe::kPartialsOffsetWords,
+                                  static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return int(e);
+  return gpu_probe_checksum_u64(w, n, first_index, out_lanes, scratch, GPU_PROBE_VARIANT_AUTO, stream);
+}

@@ -54,6 +54,8 @@ def lib() -> ctypes.CDLL:
         L.gpu_probe_triad.argtypes = [_vp, _vp, _vp, ctypes.c_double, _u64, ctypes.c_int, _vp]
         L.gpu_probe_checksum_workspace_bytes.restype = ctypes.c_size_t
         L.gpu_probe_checksum_u64.argtypes = [_vp, _u64, _u64, _vp, _vp, ctypes.c_int, _vp]
+        L.gpu_probe_checksum_u64_noalloc.argtypes = [_vp, _u64, _u64, _vp, _vp]
+        L.gpu_probe_checksum_u64_noalloc.restype = ctypes.c_int
         L.gpu_probe_triad_checksum.argtypes = [_vp, _vp, _vp, ctypes.c_double, _u64, _u64, _vp, _vp, ctypes.c_int, _vp]
         L.gpu_probe_p2p_copy.argtypes = [_vp, _vp, _u64, _vp]
         L.gpu_probe_pipeline_create.argtypes = [ctypes.POINTER(_vp), _u64, ctypes.c_int]
@@ -101,6 +103,15 @@ def checksum_u64(w: int, n: int, first_index: int, out_lanes: int, workspace: in
                  variant: int = VARIANT_AUTO, stream: int = 0) -> None:
     _check(lib().gpu_probe_checksum_u64(w, n, first_index & (2**64 - 1), out_lanes, workspace, variant, stream),
            "gpu_probe_checksum_u64")
+
+
+NOALLOC_MAX_WORDS = 1 << 34
+
+
+def checksum_u64_noalloc(w: int, n: int, first_index: int, out_lanes: int, stream: int = 0) -> None:
+    """Checksum that uses the library's built-in device scratch: no workspace argument."""
+    _check(lib().gpu_probe_checksum_u64_noalloc(w, n, first_index & (2**64 - 1), out_lanes, stream),
+           "gpu_probe_checksum_u64_noalloc")
 
 
 def triad_checksum(a: int, b: int, c: int, s: float, n: int, first_index: int, out_lanes: int, workspace: int,

@@ -52,6 +52,7 @@ extern "C" {
 #define GPU_PROBE_EALIGN (-101)    /* pointer not 8-byte aligned                  */
 #define GPU_PROBE_ETOOBIG (-102)   /* size beyond a stated maximum                */
 #define GPU_PROBE_ENOTREADY (-103) /* object used before create / after destroy   */
+#define GPU_PROBE_ETIMEDOUT (-104) /* a peer GPU never reached the exchange        */
 
 int gpu_probe_abi_version(void);
 
@@ -122,6 +123,56 @@ int gpu_probe_triad_checksum(double *a, const double *b, const double *c,
  * once peer access is enabled (NVLink 5 path).  bytes need not be a multiple of
  * 16.  (spec: SURVEY 8d "P2P copy") */
 int gpu_probe_p2p_copy(void *dst, const void *src, uint64_t bytes, void *stream);
+
+/* ---- multi-GPU: the checksum fused with its collective ----
+ * Sharded checksum: GPU g of G checksums words [g*N/G, (g+1)*N/G) of one global index
+ * space, then the 16-byte lanes are summed over GPUs.  The two-launch form is K2
+ * followed by ncclAllReduce(count=2, ncclUint64, ncclSum) (that is what
+ * kind-gpu-sim_b200/host/ and bench.py time as the baseline).  The *_exchange entry
+ * points do both in ONE kernel: the last CTA stores its lanes into a mailbox on every
+ * peer over NVLink (P2P stores + a release flag), waits for the peers' stores in its
+ * own mailbox and writes the global sum to out_lanes -- every rank ends with the same
+ * two words, bit-identical to a single-GPU checksum of the whole buffer.
+ *
+ * A gpu_probe_exchange is one rank's mailbox (1280 bytes of device memory) plus the
+ * addresses of the peers' mailboxes.
+ *   create          [blocking, ALLOCATES] on the current device.
+ *   connect_local   ranks living in one process: enables peer access both ways and
+ *                   hands raw pointers around.  xs[r] must be rank r.
+ *   export / connect_ipc   one process per GPU: export gives this rank's CUDA IPC
+ *                   handle; carry all `world` handles (rank order) to every rank by
+ *                   any host channel and pass them to connect_ipc.
+ *   status          [blocking] 0, or GPU_PROBE_ETIMEDOUT if some call's wait for a peer
+ *                   ran out (default 10 s; the kernel then writes all-ones lanes).
+ * Rules: every rank makes the same sequence of *_exchange calls (it is a collective);
+ * calls on one rank are stream-ordered (never two in flight on one mailbox); the
+ * kernels of all ranks must be able to run at the same time (do not serialise the
+ * ranks' streams behind each other). */
+typedef struct gpu_probe_exchange gpu_probe_exchange;
+#define GPU_PROBE_EXCHANGE_MAX_RANKS 16
+#define GPU_PROBE_EXCHANGE_HANDLE_BYTES 64
+
+int gpu_probe_exchange_create(gpu_probe_exchange **out, int rank, int world);
+int gpu_probe_exchange_connect_local(gpu_probe_exchange *const *xs, int world);
+int gpu_probe_exchange_export(gpu_probe_exchange *x,
+                              unsigned char handle[GPU_PROBE_EXCHANGE_HANDLE_BYTES]);
+int gpu_probe_exchange_connect_ipc(gpu_probe_exchange *x, const unsigned char *handles);
+int gpu_probe_exchange_set_timeout_ms(gpu_probe_exchange *x, uint64_t ms);
+int gpu_probe_exchange_status(gpu_probe_exchange *x);
+int gpu_probe_exchange_destroy(gpu_probe_exchange *x);
+
+/* K2 + lanes exchange in one launch.  Arguments as gpu_probe_checksum_u64; out_lanes
+ * receives the sum over ALL ranks.  Must be called with x's device current. */
+int gpu_probe_checksum_u64_exchange(const uint64_t *w, uint64_t n, uint64_t first_index,
+                                    uint64_t *out_lanes, void *workspace, int variant,
+                                    gpu_probe_exchange *x, void *stream);
+
+/* Fused K1+K2 + lanes exchange in one launch (24 B/element, no second kernel, no
+ * NCCL launch).  Arguments as gpu_probe_triad_checksum. */
+int gpu_probe_triad_checksum_exchange(double *a, const double *b, const double *c,
+                                      double s, uint64_t n, uint64_t first_index,
+                                      uint64_t *out_lanes, void *workspace, int variant,
+                                      gpu_probe_exchange *x, void *stream);
 
 /* ---- host-buffer pipeline (the end-to-end call for a host that holds b, c) ----
  * create [blocking, ALLOCATES]: device staging for `depth` chunks of

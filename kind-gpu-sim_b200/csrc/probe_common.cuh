@@ -113,13 +113,105 @@ constexpr int kPartialsOffsetWords = 32;  // keep the ticket on its own 256-B li
 constexpr size_t kWorkspaceBytes =
     sizeof(uint64_t) * (kPartialsOffsetWords + 2 * size_t(kMaxPartialCtas));
 
+// ---- lanes exchange over peer memory (fused checksum + collective) ------------
+// The path's one collective is a 16-byte sum.  Instead of a separate NCCL launch the
+// last CTA of the checksum kernel stores this GPU's lanes straight into a mailbox slot
+// on every peer (NVLink P2P stores), then waits for the peers' slots in its OWN mailbox
+// and adds them.  Wrapping u64 sums commute, so arrival order cannot change a bit.
+//
+// Mailbox layout (one per GPU, uint64 words; allocated by gpu_probe_exchange_create):
+//   word 0         : call counter of this GPU (local only)
+//   word 1         : sticky error flag (local only; 1 = a peer never arrived)
+//   words 32 ..    : slots[2][kMaxRanks] of {lane0, lane1, epoch, pad}; the buffer is
+//                    chosen by epoch parity.  Two buffers suffice: a rank can only
+//                    start call k+2 after every peer has written call k+1, which each
+//                    peer does after it finished reading call k.
+constexpr int kMaxRanks = 16;
+constexpr int kSlotWords = 4;
+constexpr int kMailboxSlotsOffsetWords = 32;
+constexpr size_t kMailboxBytes = sizeof(uint64_t) * (kMailboxSlotsOffsetWords + 2 * kMaxRanks * kSlotWords);
+
+struct ExchangeArgs {           // passed to kernels by value; world == 0: no exchange
+  uint64_t *mailbox[kMaxRanks]; // mailbox[p]: rank p's mailbox as THIS GPU addresses it
+  int rank, world;
+  unsigned long long timeout_ns;
+};
+
+__device__ __forceinline__ void st_release_sys(uint64_t *p, uint64_t v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void st_relaxed_sys(uint64_t *p, uint64_t v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint64_t ld_acquire_sys(const uint64_t *p) {
+  uint64_t v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint64_t ld_relaxed_sys(const uint64_t *p) {
+  uint64_t v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// Called by every thread of the LAST CTA; (s0, s1) = this GPU's final lanes, valid in
+// thread 0.  Writes the sum over all ranks to out[0..1].  `smem` holds >= 4 words.
+__device__ __forceinline__ void exchange_lanes(uint64_t s0, uint64_t s1, const ExchangeArgs &x,
+                                               uint64_t *__restrict__ out, uint64_t *smem) {
+  uint64_t *mine = x.mailbox[x.rank];
+  if (threadIdx.x == 0) {
+    const uint64_t epoch = mine[0] + 1;  // calls on one GPU are stream-ordered: no race
+    mine[0] = epoch;
+    smem[0] = s0; smem[1] = s1; smem[2] = epoch;
+  }
+  __syncthreads();
+  if (threadIdx.x >= 32) return;  // warp 0 talks to the peers, one lane per rank
+  const uint64_t epoch = smem[2];
+  const size_t buf = kMailboxSlotsOffsetWords + size_t(epoch & 1) * kMaxRanks * kSlotWords;
+  uint64_t v0 = 0, v1 = 0;
+  int failed = 0;
+  const int p = threadIdx.x;
+  if (p < x.world) {
+    uint64_t *theirs = x.mailbox[p] + buf + size_t(x.rank) * kSlotWords;  // my slot in p's mailbox
+    st_relaxed_sys(theirs, smem[0]);
+    st_relaxed_sys(theirs + 1, smem[1]);
+    st_release_sys(theirs + 2, epoch);  // release: the two lanes are visible before the flag
+    const uint64_t *slot = mine + buf + size_t(p) * kSlotWords;  // p's slot in my mailbox
+    const unsigned long long t0 = global_ns();
+    while (ld_acquire_sys(slot + 2) != epoch) {
+      if (global_ns() - t0 > x.timeout_ns) { failed = 1; break; }
+    }
+    v0 = ld_relaxed_sys(slot);
+    v1 = ld_relaxed_sys(slot + 1);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    v0 += __shfl_xor_sync(0xffffffffu, v0, o);
+    v1 += __shfl_xor_sync(0xffffffffu, v1, o);
+    failed |= __shfl_xor_sync(0xffffffffu, failed, o);
+  }
+  if (threadIdx.x == 0) {
+    if (failed) { mine[1] = 1; v0 = ~0ull; v1 = ~0ull; }  // loud: no plausible lanes on a timeout
+    out[0] = v0;
+    out[1] = v1;
+  }
+}
+
 // Every CTA publishes its partial; the last one to take a ticket adds them up,
-// applies the global-index fix-up and overwrites out[0..1].  Wrapping u64 sums are
-// associative and commutative, so the order CTAs finish in cannot change a bit.
+// applies the global-index fix-up and overwrites out[0..1] -- with this GPU's lanes,
+// or, when an exchange is attached, with the sum over all ranks' lanes.
+// Wrapping u64 sums are associative and commutative, so the order CTAs (or GPUs)
+// finish in cannot change a bit.
 //   lane1 was accumulated with LOCAL indices k; sum w*(2(f+k)+1) = lane1 + 2f*lane0.
 __device__ __forceinline__ void finish_lanes(Lanes mine, uint64_t first_index,
                                              uint64_t *__restrict__ out,
-                                             uint64_t *__restrict__ ws, uint64_t *smem) {
+                                             uint64_t *__restrict__ ws, uint64_t *smem,
+                                             const ExchangeArgs &x) {
   __shared__ bool is_last;
   Lanes blk = block_sum(mine, smem);
   if (threadIdx.x == 0) {
@@ -140,10 +232,13 @@ __device__ __forceinline__ void finish_lanes(Lanes mine, uint64_t first_index,
     acc.s1 += __ldcg(part + 1);
   }
   acc = block_sum(acc, smem);
-  if (threadIdx.x == 0) {
-    out[0] = acc.s0;
-    out[1] = acc.s1 + 2 * first_index * acc.s0;
-    ws[0] = 0;  // ticket back to zero for the next launch on this workspace
+  const uint64_t l0 = acc.s0, l1 = acc.s1 + 2 * first_index * acc.s0;
+  if (threadIdx.x == 0) ws[0] = 0;  // ticket back to zero for the next launch on this workspace
+  if (x.world > 0) {
+    exchange_lanes(l0, l1, x, out, smem);
+  } else if (threadIdx.x == 0) {
+    out[0] = l0;
+    out[1] = l1;
   }
 }
 

@@ -17,6 +17,7 @@
 #include <cuda_runtime.h>
 
 #include "probe_common.cuh"
+#include "probe_launch.h"
 #include "probe_tma.cuh"
 
 namespace probe {
@@ -87,7 +88,7 @@ init_fill_scalar(double *__restrict__ dst, uint64_t n, uint64_t first, uint64_t 
 template <typename V, int U, bool LANES>
 __global__ void __launch_bounds__(kThreads)
 triad_vec(V *__restrict__ a, const V *__restrict__ b, const V *__restrict__ c, double s, uint64_t nvec,
-          uint64_t n, uint64_t first, uint64_t *__restrict__ out, uint64_t *__restrict__ ws) {
+          uint64_t n, uint64_t first, uint64_t *__restrict__ out, uint64_t *__restrict__ ws, const ExchangeArgs x) {
   constexpr int E = lanes_of<V>::E;
   __shared__ uint64_t red[64];
   Lanes acc{0, 0};
@@ -127,13 +128,13 @@ triad_vec(V *__restrict__ a, const V *__restrict__ b, const V *__restrict__ c, d
     reinterpret_cast<double *>(a)[k] = r;
     if (LANES) acc.add(bits(r), 2 * k + 1);
   }
-  if (LANES) finish_lanes(acc, first, out, ws, red);
+  if (LANES) finish_lanes(acc, first, out, ws, red, x);
 }
 
 template <bool LANES>
 __global__ void __launch_bounds__(kThreads)
 triad_scalar(double *__restrict__ a, const double *__restrict__ b, const double *__restrict__ c, double s,
-             uint64_t n, uint64_t first, uint64_t *__restrict__ out, uint64_t *__restrict__ ws) {
+             uint64_t n, uint64_t first, uint64_t *__restrict__ out, uint64_t *__restrict__ ws, const ExchangeArgs x) {
   __shared__ uint64_t red[64];
   Lanes acc{0, 0};
   for (uint64_t k = blockIdx.x * uint64_t(kThreads) + threadIdx.x; k < n; k += uint64_t(gridDim.x) * kThreads) {
@@ -141,7 +142,7 @@ triad_scalar(double *__restrict__ a, const double *__restrict__ b, const double 
     a[k] = r;
     if (LANES) acc.add(bits(r), 2 * k + 1);
   }
-  if (LANES) finish_lanes(acc, first, out, ws, red);
+  if (LANES) finish_lanes(acc, first, out, ws, red, x);
 }
 
 // ---------------------------------------------------------------------------
@@ -150,7 +151,7 @@ triad_scalar(double *__restrict__ a, const double *__restrict__ b, const double 
 template <typename V, int U>
 __global__ void __launch_bounds__(kThreads)
 checksum_vec(const V *__restrict__ w, uint64_t nvec, uint64_t n, uint64_t first, uint64_t *__restrict__ out,
-             uint64_t *__restrict__ ws) {
+             uint64_t *__restrict__ ws, const ExchangeArgs x) {
   constexpr int E = lanes_of<V>::E;
   __shared__ uint64_t red[64];
   Lanes acc{0, 0};
@@ -176,17 +177,17 @@ checksum_vec(const V *__restrict__ w, uint64_t nvec, uint64_t n, uint64_t first,
     const uint64_t k = done + threadIdx.x;
     acc.add(reinterpret_cast<const uint64_t *>(w)[k], 2 * k + 1);
   }
-  finish_lanes(acc, first, out, ws, red);
+  finish_lanes(acc, first, out, ws, red, x);
 }
 
 __global__ void __launch_bounds__(kThreads)
 checksum_scalar(const uint64_t *__restrict__ w, uint64_t n, uint64_t first, uint64_t *__restrict__ out,
-                uint64_t *__restrict__ ws) {
+                uint64_t *__restrict__ ws, const ExchangeArgs x) {
   __shared__ uint64_t red[64];
   Lanes acc{0, 0};
   for (uint64_t k = blockIdx.x * uint64_t(kThreads) + threadIdx.x; k < n; k += uint64_t(gridDim.x) * kThreads)
     acc.add(w[k], 2 * k + 1);
-  finish_lanes(acc, first, out, ws, red);
+  finish_lanes(acc, first, out, ws, red, x);
 }
 
 // ---------------------------------------------------------------------------
@@ -206,7 +207,7 @@ struct TriadTmaSmem {
 template <int TILE, int S, bool LANES>
 __global__ void __launch_bounds__(kThreads)
 triad_tma(double *__restrict__ a, const double *__restrict__ b, const double *__restrict__ c, double s, uint64_t n,
-          uint64_t first, uint64_t *__restrict__ out, uint64_t *__restrict__ ws) {
+          uint64_t first, uint64_t *__restrict__ out, uint64_t *__restrict__ ws, const ExchangeArgs x) {
   static_assert(TILE % (2 * kThreads) == 0, "tile must split into one f64x2 per thread per pass");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   double *sb = reinterpret_cast<double *>(smem_raw);
@@ -271,7 +272,7 @@ triad_tma(double *__restrict__ a, const double *__restrict__ b, const double *__
       if (LANES) acc.add(bits(r), 2 * k + 1);
     }
   }
-  if (LANES) finish_lanes(acc, first, out, ws, red);
+  if (LANES) finish_lanes(acc, first, out, ws, red, x);
 }
 
 template <int TILE, int S>
@@ -282,7 +283,7 @@ struct ChecksumTmaSmem {
 template <int TILE, int S>
 __global__ void __launch_bounds__(kThreads)
 checksum_tma(const uint64_t *__restrict__ w, uint64_t n, uint64_t first, uint64_t *__restrict__ out,
-             uint64_t *__restrict__ ws) {
+             uint64_t *__restrict__ ws, const ExchangeArgs x) {
   static_assert(TILE % (2 * kThreads) == 0, "tile must split into one u64x2 per thread per pass");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   uint64_t *sw = reinterpret_cast<uint64_t *>(smem_raw);
@@ -329,7 +330,7 @@ checksum_tma(const uint64_t *__restrict__ w, uint64_t n, uint64_t first, uint64_
   }
   if (blockIdx.x == gridDim.x - 1)
     for (uint64_t k = ntiles * TILE + tid; k < n; k += kThreads) acc.add(w[k], 2 * k + 1);
-  finish_lanes(acc, first, out, ws, red);
+  finish_lanes(acc, first, out, ws, red, x);
 }
 
 // ---------------------------------------------------------------------------
@@ -475,7 +476,7 @@ constexpr int kLdgChecksumCtasPerSm = 6;
 
 template <bool LANES>
 static int launch_triad(double *a, const double *b, const double *c, double s, uint64_t n, uint64_t first,
-                        uint64_t *out, uint64_t *ws, int variant, cudaStream_t st) {
+                        uint64_t *out, uint64_t *ws, int variant, cudaStream_t st, const ExchangeArgs &x) {
   if (variant == GPU_PROBE_VARIANT_AUTO) variant = g_auto_triad;
   const bool al16 = aligned(a, 16) && aligned(b, 16) && aligned(c, 16);
   const bool al32 = aligned(a, 32) && aligned(b, 32) && aligned(c, 32);
@@ -484,14 +485,14 @@ static int launch_triad(double *a, const double *b, const double *c, double s, u
   if (!al16) {
     auto k = triad_scalar<LANES>;
     if ((rc = persistent_grid(k, 0, (n + kThreads - 1) / kThreads, &grid))) return rc;
-    k<<<grid, kThreads, 0, st>>>(a, b, c, s, n, first, out, ws);
+    k<<<grid, kThreads, 0, st>>>(a, b, c, s, n, first, out, ws, x);
     return launch_rc();
   }
   if (variant == GPU_PROBE_VARIANT_TMA) {
     auto k = triad_tma<kTriadTile, kTriadStages, LANES>;
     constexpr size_t smem = TriadTmaSmem<kTriadTile, kTriadStages>::kBytes;
     if ((rc = persistent_grid(k, smem, n / kTriadTile, &grid, kTriadCtasPerSm))) return rc;
-    k<<<grid, kThreads, smem, st>>>(a, b, c, s, n, first, out, ws);
+    k<<<grid, kThreads, smem, st>>>(a, b, c, s, n, first, out, ws, x);
     return launch_rc();
   }
   if (variant == GPU_PROBE_VARIANT_LDG256 && al32) {
@@ -500,7 +501,7 @@ static int launch_triad(double *a, const double *b, const double *c, double s, u
     const uint64_t nvec = n / 4;
     if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid, kLdgTriadCtasPerSm))) return rc;
     k<<<grid, kThreads, 0, st>>>(reinterpret_cast<f64x4 *>(a), reinterpret_cast<const f64x4 *>(b),
-                                 reinterpret_cast<const f64x4 *>(c), s, nvec, n, first, out, ws);
+                                 reinterpret_cast<const f64x4 *>(c), s, nvec, n, first, out, ws, x);
     return launch_rc();
   }
   {
@@ -509,13 +510,63 @@ static int launch_triad(double *a, const double *b, const double *c, double s, u
     const uint64_t nvec = n / 2;
     if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid, kLdgTriadCtasPerSm))) return rc;
     k<<<grid, kThreads, 0, st>>>(reinterpret_cast<f64x2 *>(a), reinterpret_cast<const f64x2 *>(b),
-                                 reinterpret_cast<const f64x2 *>(c), s, nvec, n, first, out, ws);
+                                 reinterpret_cast<const f64x2 *>(c), s, nvec, n, first, out, ws, x);
     return launch_rc();
   }
 }
 
 static int check_variant(int v) {
   return (v >= GPU_PROBE_VARIANT_AUTO && v <= GPU_PROBE_VARIANT_LDG256) ? 0 : GPU_PROBE_EINVAL;
+}
+
+// Argument checks + launch of K2; `x.world > 0` attaches the lanes exchange (probe_exchange.cu).
+int checked_checksum(const uint64_t *w, uint64_t n, uint64_t first_index, uint64_t *out_lanes, void *workspace,
+                     int variant, void *stream, const ExchangeArgs &x) {
+  if (check_variant(variant)) return GPU_PROBE_EINVAL;
+  if (!out_lanes || !workspace || (!w && n)) return GPU_PROBE_EINVAL;
+  if (!aligned(w, 8) || !aligned(out_lanes, 8) || !aligned(workspace, 8)) return GPU_PROBE_EALIGN;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  uint64_t *ws = static_cast<uint64_t *>(workspace);
+  if (variant == GPU_PROBE_VARIANT_AUTO) variant = g_auto_checksum;
+  unsigned grid = 1;
+  int rc;
+  if (!aligned(w, 16)) {
+    if ((rc = persistent_grid(checksum_scalar, 0, (n + kThreads - 1) / kThreads, &grid))) return rc;
+    checksum_scalar<<<grid, kThreads, 0, st>>>(w, n, first_index, out_lanes, ws, x);
+    return launch_rc();
+  }
+  if (variant == GPU_PROBE_VARIANT_TMA) {
+    auto k = checksum_tma<kChecksumTile, kChecksumStages>;
+    constexpr size_t smem = ChecksumTmaSmem<kChecksumTile, kChecksumStages>::kBytes;
+    if ((rc = persistent_grid(k, smem, n / kChecksumTile, &grid, kChecksumCtasPerSm))) return rc;
+    k<<<grid, kThreads, smem, st>>>(w, n, first_index, out_lanes, ws, x);
+    return launch_rc();
+  }
+  if (variant == GPU_PROBE_VARIANT_LDG256 && aligned(w, 32)) {
+    constexpr int U = 4;
+    auto k = checksum_vec<u64x4, U>;
+    const uint64_t nvec = n / 4;
+    if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid, kLdgChecksumCtasPerSm))) return rc;
+    k<<<grid, kThreads, 0, st>>>(reinterpret_cast<const u64x4 *>(w), nvec, n, first_index, out_lanes, ws, x);
+    return launch_rc();
+  }
+  constexpr int U = 8;
+  auto k = checksum_vec<u64x2, U>;
+  const uint64_t nvec = n / 2;
+  if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid, kLdgChecksumCtasPerSm))) return rc;
+  k<<<grid, kThreads, 0, st>>>(reinterpret_cast<const u64x2 *>(w), nvec, n, first_index, out_lanes, ws, x);
+  return launch_rc();
+}
+
+// Argument checks + launch of the fused K1+K2.
+int checked_triad_checksum(double *a, const double *b, const double *c, double s, uint64_t n, uint64_t first_index,
+                           uint64_t *out_lanes, void *workspace, int variant, void *stream, const ExchangeArgs &x) {
+  if (check_variant(variant)) return GPU_PROBE_EINVAL;
+  if (!out_lanes || !workspace || (n && (!a || !b || !c))) return GPU_PROBE_EINVAL;
+  if (!aligned(a, 8) || !aligned(b, 8) || !aligned(c, 8) || !aligned(out_lanes, 8) || !aligned(workspace, 8))
+    return GPU_PROBE_EALIGN;
+  return launch_triad<true>(a, b, c, s, n, first_index, out_lanes, static_cast<uint64_t *>(workspace), variant,
+                            static_cast<cudaStream_t>(stream), x);
 }
 
 }  // namespace probe
@@ -530,7 +581,7 @@ extern "C" {
 int gpu_probe_abi_version(void) { return GPU_PROBE_ABI_VERSION; }
 
 const char *gpu_probe_kernel_info(void) {
-  return "gpu-probe abi=1 arch=sm_100a kernels=init_fill,triad,checksum_u64,triad_checksum,p2p_copy "
+  return "gpu-probe abi=1 arch=sm_100a kernels=init_fill,triad,checksum_u64,triad_checksum,p2p_copy,lanes_exchange "
          "variants=ldg128,tma_bulk,ldg256 cpu_fallback=none";
 }
 
@@ -541,7 +592,8 @@ const char *gpu_probe_error_string(int rc) {
     case GPU_PROBE_EINVAL: return "gpu_probe: invalid argument (null pointer, unknown variant or bad size)";
     case GPU_PROBE_EALIGN: return "gpu_probe: pointer is not 8-byte aligned";
     case GPU_PROBE_ETOOBIG: return "gpu_probe: size exceeds the stated maximum of this entry point";
-    case GPU_PROBE_ENOTREADY: return "gpu_probe: object not created or already destroyed";
+    case GPU_PROBE_ENOTREADY: return "gpu_probe: object not created, not connected or already destroyed";
+    case GPU_PROBE_ETIMEDOUT: return "gpu_probe: a peer GPU never reached the lanes exchange (timed out)";
   }
   if (rc > -100) return "gpu_probe: NCCL error (value is -ncclResult_t)";
   return "gpu_probe: unknown error code";
@@ -572,57 +624,20 @@ int gpu_probe_triad(double *a, const double *b, const double *c, double s, uint6
   if (n == 0) return 0;
   if (!a || !b || !c) return GPU_PROBE_EINVAL;
   if (!aligned(a, 8) || !aligned(b, 8) || !aligned(c, 8)) return GPU_PROBE_EALIGN;
-  return launch_triad<false>(a, b, c, s, n, 0, nullptr, nullptr, variant, static_cast<cudaStream_t>(stream));
+  return launch_triad<false>(a, b, c, s, n, 0, nullptr, nullptr, variant, static_cast<cudaStream_t>(stream),
+                             ExchangeArgs{});
 }
 
 size_t gpu_probe_checksum_workspace_bytes(void) { return kWorkspaceBytes; }
 
 int gpu_probe_checksum_u64(const uint64_t *w, uint64_t n, uint64_t first_index, uint64_t *out_lanes, void *workspace,
                            int variant, void *stream) {
-  if (check_variant(variant)) return GPU_PROBE_EINVAL;
-  if (!out_lanes || !workspace || (!w && n)) return GPU_PROBE_EINVAL;
-  if (!aligned(w, 8) || !aligned(out_lanes, 8) || !aligned(workspace, 8)) return GPU_PROBE_EALIGN;
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  uint64_t *ws = static_cast<uint64_t *>(workspace);
-  if (variant == GPU_PROBE_VARIANT_AUTO) variant = g_auto_checksum;
-  unsigned grid = 1;
-  int rc;
-  if (!aligned(w, 16)) {
-    if ((rc = persistent_grid(checksum_scalar, 0, (n + kThreads - 1) / kThreads, &grid))) return rc;
-    checksum_scalar<<<grid, kThreads, 0, st>>>(w, n, first_index, out_lanes, ws);
-    return launch_rc();
-  }
-  if (variant == GPU_PROBE_VARIANT_TMA) {
-    auto k = checksum_tma<kChecksumTile, kChecksumStages>;
-    constexpr size_t smem = ChecksumTmaSmem<kChecksumTile, kChecksumStages>::kBytes;
-    if ((rc = persistent_grid(k, smem, n / kChecksumTile, &grid, kChecksumCtasPerSm))) return rc;
-    k<<<grid, kThreads, smem, st>>>(w, n, first_index, out_lanes, ws);
-    return launch_rc();
-  }
-  if (variant == GPU_PROBE_VARIANT_LDG256 && aligned(w, 32)) {
-    constexpr int U = 4;
-    auto k = checksum_vec<u64x4, U>;
-    const uint64_t nvec = n / 4;
-    if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid, kLdgChecksumCtasPerSm))) return rc;
-    k<<<grid, kThreads, 0, st>>>(reinterpret_cast<const u64x4 *>(w), nvec, n, first_index, out_lanes, ws);
-    return launch_rc();
-  }
-  constexpr int U = 8;
-  auto k = checksum_vec<u64x2, U>;
-  const uint64_t nvec = n / 2;
-  if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid, kLdgChecksumCtasPerSm))) return rc;
-  k<<<grid, kThreads, 0, st>>>(reinterpret_cast<const u64x2 *>(w), nvec, n, first_index, out_lanes, ws);
-  return launch_rc();
+  return checked_checksum(w, n, first_index, out_lanes, workspace, variant, stream, ExchangeArgs{});
 }
 
 int gpu_probe_triad_checksum(double *a, const double *b, const double *c, double s, uint64_t n, uint64_t first_index,
                              uint64_t *out_lanes, void *workspace, int variant, void *stream) {
-  if (check_variant(variant)) return GPU_PROBE_EINVAL;
-  if (!out_lanes || !workspace || (n && (!a || !b || !c))) return GPU_PROBE_EINVAL;
-  if (!aligned(a, 8) || !aligned(b, 8) || !aligned(c, 8) || !aligned(out_lanes, 8) || !aligned(workspace, 8))
-    return GPU_PROBE_EALIGN;
-  return launch_triad<true>(a, b, c, s, n, first_index, out_lanes, static_cast<uint64_t *>(workspace), variant,
-                            static_cast<cudaStream_t>(stream));
+  return checked_triad_checksum(a, b, c, s, n, first_index, out_lanes, workspace, variant, stream, ExchangeArgs{});
 }
 
 int gpu_probe_p2p_copy(void *dst, const void *src, uint64_t bytes, void *stream) {

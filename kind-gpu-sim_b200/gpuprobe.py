@@ -22,7 +22,8 @@ SCALAR = 3.0
 VARIANT_AUTO, VARIANT_LDG, VARIANT_TMA, VARIANT_LDG256 = -1, 0, 1, 2
 VARIANTS = {"auto": VARIANT_AUTO, "ldg128": VARIANT_LDG, "tma": VARIANT_TMA, "ldg256": VARIANT_LDG256}
 
-EINVAL, EALIGN, ETOOBIG, ENOTREADY = -100, -101, -102, -103
+EINVAL, EALIGN, ETOOBIG, ENOTREADY, ETIMEDOUT = -100, -101, -102, -103, -104
+EXCHANGE_MAX_RANKS, EXCHANGE_HANDLE_BYTES = 16, 64
 
 _u64 = ctypes.c_uint64
 _vp = ctypes.c_void_p
@@ -62,6 +63,21 @@ def lib() -> ctypes.CDLL:
         L.gpu_probe_pipeline_run_host.argtypes = [_vp, _vp, _vp, _vp, ctypes.c_double, _u64, _u64,
                                                   ctypes.POINTER(_u64)]
         L.gpu_probe_pipeline_destroy.argtypes = [_vp]
+        L.gpu_probe_exchange_create.argtypes = [ctypes.POINTER(_vp), ctypes.c_int, ctypes.c_int]
+        L.gpu_probe_exchange_connect_local.argtypes = [ctypes.POINTER(_vp), ctypes.c_int]
+        L.gpu_probe_exchange_export.argtypes = [_vp, ctypes.c_char_p]
+        L.gpu_probe_exchange_connect_ipc.argtypes = [_vp, ctypes.c_char_p]
+        L.gpu_probe_exchange_set_timeout_ms.argtypes = [_vp, _u64]
+        L.gpu_probe_exchange_status.argtypes = [_vp]
+        L.gpu_probe_exchange_destroy.argtypes = [_vp]
+        L.gpu_probe_checksum_u64_exchange.argtypes = [_vp, _u64, _u64, _vp, _vp, ctypes.c_int, _vp, _vp]
+        L.gpu_probe_triad_checksum_exchange.argtypes = [_vp, _vp, _vp, ctypes.c_double, _u64, _u64, _vp, _vp,
+                                                        ctypes.c_int, _vp, _vp]
+        for name in ("gpu_probe_exchange_create", "gpu_probe_exchange_connect_local", "gpu_probe_exchange_export",
+                     "gpu_probe_exchange_connect_ipc", "gpu_probe_exchange_set_timeout_ms", "gpu_probe_exchange_status",
+                     "gpu_probe_exchange_destroy", "gpu_probe_checksum_u64_exchange",
+                     "gpu_probe_triad_checksum_exchange"):
+            getattr(L, name).restype = ctypes.c_int
         for name in ("gpu_probe_init_fill", "gpu_probe_triad", "gpu_probe_checksum_u64", "gpu_probe_triad_checksum",
                      "gpu_probe_p2p_copy", "gpu_probe_pipeline_create", "gpu_probe_pipeline_run_host",
                      "gpu_probe_pipeline_destroy"):
@@ -148,3 +164,50 @@ class Pipeline:
 
     def __exit__(self, *exc):
         self.close()
+
+
+class Exchange:
+    """One rank's mailbox for the fused checksum + lanes exchange (gpu_probe_exchange_*).
+    Create with the rank's device current; then either Exchange.connect_local([...]) for
+    ranks in one process, or export_handle() / connect_ipc(all_handles) across processes."""
+
+    def __init__(self, rank: int, world: int):
+        self._h = _vp()
+        self.rank, self.world = rank, world
+        _check(lib().gpu_probe_exchange_create(ctypes.byref(self._h), rank, world), "gpu_probe_exchange_create")
+
+    @staticmethod
+    def connect_local(xs: "list[Exchange]") -> None:
+        arr = (_vp * len(xs))(*[x._h for x in xs])
+        _check(lib().gpu_probe_exchange_connect_local(arr, len(xs)), "gpu_probe_exchange_connect_local")
+
+    def export_handle(self) -> bytes:
+        buf = ctypes.create_string_buffer(EXCHANGE_HANDLE_BYTES)
+        _check(lib().gpu_probe_exchange_export(self._h, buf), "gpu_probe_exchange_export")
+        return buf.raw
+
+    def connect_ipc(self, handles: bytes) -> None:
+        if len(handles) != self.world * EXCHANGE_HANDLE_BYTES:
+            raise ValueError("need world x 64 bytes of handles, in rank order")
+        _check(lib().gpu_probe_exchange_connect_ipc(self._h, handles), "gpu_probe_exchange_connect_ipc")
+
+    def set_timeout_ms(self, ms: int) -> None:
+        _check(lib().gpu_probe_exchange_set_timeout_ms(self._h, ms), "gpu_probe_exchange_set_timeout_ms")
+
+    def status(self) -> int:
+        return int(lib().gpu_probe_exchange_status(self._h))
+
+    def checksum_u64(self, w: int, n: int, first_index: int, out_lanes: int, workspace: int,
+                     variant: int = VARIANT_AUTO, stream: int = 0) -> None:
+        _check(lib().gpu_probe_checksum_u64_exchange(w, n, first_index & (2**64 - 1), out_lanes, workspace, variant,
+                                                     self._h, stream), "gpu_probe_checksum_u64_exchange")
+
+    def triad_checksum(self, a: int, b: int, c: int, s: float, n: int, first_index: int, out_lanes: int,
+                       workspace: int, variant: int = VARIANT_AUTO, stream: int = 0) -> None:
+        _check(lib().gpu_probe_triad_checksum_exchange(a, b, c, s, n, first_index & (2**64 - 1), out_lanes, workspace,
+                                                       variant, self._h, stream), "gpu_probe_triad_checksum_exchange")
+
+    def close(self) -> None:
+        if self._h:
+            _check(lib().gpu_probe_exchange_destroy(self._h), "gpu_probe_exchange_destroy")
+            self._h = _vp()

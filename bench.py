@@ -204,7 +204,7 @@ def workload_config(args, world):
         "workload": "BASELINE.json configs[1]: 1-GPU probe pod, 4 GiB stream-triad + uint64 checksum vs CPU reference"
                     + ("" if world == 1 else f" (replicated per GPU, {world} ranks; lanes exchanged every step)"),
         "elements_per_gpu": 1 << args.log2n, "bytes_per_array_per_gpu": 8 << args.log2n,
-        "step": "triad(24 B/elem) + checksum_u64(8 B/elem)" + ("" if world == 1 else " + lanes allreduce(16 B)"),
+        "step": "triad(24 B/elem) + checksum_u64(8 B/elem)" + ("" if world == 1 else " + lanes allreduce(16 B, fused into the checksum kernel)"),
         "variant": args.variant,
         "l2": "inputs are 3 x 4 GiB per GPU >> 126 MB L2, so no flush between iterations",
         "parallelism": f"shard{world}" if world > 1 else "single",
@@ -248,12 +248,42 @@ def run_ours(args, rank, local_rank, world):
         if dist is not None:
             dist.barrier()
 
-    def step(ev=None):
+    # N > 1: the path's one collective (16 bytes of lanes).  Product path: fused into the
+    # checksum kernel over NVLink peer stores (gpu_probe_checksum_u64_exchange); the mailbox
+    # addresses travel between the ranks as CUDA IPC handles over torch.distributed.
+    # NCCL (int64 allreduce after K2) is timed beside it as the two-launch baseline.
+    xchg, combine = None, "none (single GPU)"
+    if dist is not None and args.combine == "exchange":
+        try:
+            xchg = gpuprobe.Exchange(rank, world)
+            mine = torch.tensor(list(xchg.export_handle()), dtype=torch.uint8, device="cuda")
+            allh = [torch.empty_like(mine) for _ in range(world)]
+            dist.all_gather(allh, mine)
+            xchg.connect_ipc(b"".join(bytes(h.cpu().tolist()) for h in allh))
+            ok = torch.ones(1, dtype=torch.int32, device="cuda")
+        except gpuprobe.ProbeError as e:
+            print(f"bench.py: rank {rank}: CUDA IPC exchange unavailable ({e}); combining with NCCL", file=sys.stderr)
+            ok = torch.zeros(1, dtype=torch.int32, device="cuda")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 0:
+            xchg = None
+        combine = ("p2p_exchange_fused (gpu_probe_checksum_u64_exchange, CUDA IPC mailboxes)" if xchg is not None
+                   else "nccl_allreduce_int64 (CUDA IPC unavailable on this box)")
+        dist.barrier()
+    elif dist is not None:
+        combine = "nccl_allreduce_int64"
+
+    def step(ev=None, use_nccl=False):
         if ev:
             ev[0].record()
         gpuprobe.triad(a.data_ptr(), b.data_ptr(), c.data_ptr(), gpuprobe.SCALAR, n, variant, st)
         if ev:
             ev[1].record()
+        if xchg is not None and not use_nccl:  # every rank's `total` = lanes of the whole index space
+            xchg.checksum_u64(a.data_ptr(), n, first, total.data_ptr(), ws.data_ptr(), variant, st)
+            if ev:
+                ev[2].record()
+            return
         gpuprobe.checksum_u64(a.data_ptr(), n, first, lanes.data_ptr(), ws.data_ptr(), variant, st)
         if ev:
             ev[2].record()
@@ -279,12 +309,33 @@ def run_ours(args, rank, local_rank, world):
     ms_total = t_start.elapsed_time(t_end)
     triad_ms = [e[0].elapsed_time(e[1]) for e in evs]
     csum_ms = [e[1].elapsed_time(e[2]) for e in evs]
-    my_lanes = tuple(int(x) for x in lanes.cpu().numpy().view(np.uint64))
+    my_lanes = tuple(int(x) for x in (lanes if dist is None else total).cpu().numpy().view(np.uint64))
 
+    nccl_ms_step = None
     if dist is not None:
         t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total = float(t.item())
+        if xchg is not None:
+            if xchg.status() != 0:
+                raise SystemExit(f"bench.py: rank {rank}: lanes exchange timed out")
+            # the same step with the two-launch NCCL combine, for comparison only
+            k2 = min(args.steps, 20)
+            for _ in range(3):
+                step(use_nccl=True)
+            barrier()
+            torch.cuda.synchronize()
+            t_start.record()
+            for _ in range(k2):
+                step(use_nccl=True)
+            t_end.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([t_start.elapsed_time(t_end) / k2], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            nccl_ms_step = float(t.item())
+            nccl_lanes = tuple(int(x) for x in total.cpu().numpy().view(np.uint64))
+            if nccl_lanes != my_lanes:
+                raise SystemExit(f"bench.py: rank {rank}: exchange lanes {my_lanes} != NCCL lanes {nccl_lanes}")
     ms_step = ms_total / args.steps
     step_bytes = (BYTES_TRIAD + BYTES_CHECKSUM) * n * world
     value = step_bytes / (ms_step / 1e3) / 1e9
@@ -327,6 +378,22 @@ def run_ours(args, rank, local_rank, world):
         }
         if nvlink is not None:
             line["nvlink"] = nvlink
+        if dist is not None:
+            line["combine"] = {"how": combine, "ms_per_step_with_nccl_combine": nccl_ms_step,
+                               "launches_per_step": 2 if xchg is not None else 4}
+            line["gpu_launches"] = (2 if xchg is not None else 4) * args.steps
+            # weak scaling over one global index space: the combined lanes have a known answer
+            try:
+                with open(os.path.join(ROOT, "tests", "golden", "probe_golden.json")) as f:
+                    pow2 = json.load(f)["pow2_lanes"]
+                want = tuple(int(v, 16) for v in pow2[(n * world).bit_length() - 1]) if (n * world) & (n * world - 1) == 0 else None
+            except Exception:
+                want = None
+            line["parity"] = {"combined_lanes_equal_golden": (want == my_lanes) if want else None,
+                              "checked": f"{world} shards x 2^{args.log2n} elements, golden = tests/golden/probe_golden.json pow2_lanes"}
+            if want is not None and want != my_lanes:
+                print(json.dumps(line), flush=True)
+                raise SystemExit("bench.py: combined GPU lanes differ from the golden lanes")
         if world == 1 and not args.no_cpu:
             import oracle
             want = oracle.stream_lanes(n, first)
@@ -342,6 +409,8 @@ def run_ours(args, rank, local_rank, world):
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.barrier()
+        if xchg is not None:
+            xchg.close()
         dist.destroy_process_group()
 
 
@@ -437,6 +506,8 @@ def main():
     ap.add_argument("--cpu-log2n", type=int, default=28, help="cpu_baseline sample size (elements per array)")
     ap.add_argument("--ref-log2n", type=int, default=28, help="--impl reference sample per step")
     ap.add_argument("--sweep-log2max", type=int, default=30)
+    ap.add_argument("--combine", choices=["exchange", "nccl"], default="exchange",
+                    help="N>1: how the 16-byte lanes are summed over ranks (fused P2P exchange, or NCCL)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / parity leg")
     args = ap.parse_args()

@@ -1,0 +1,82 @@
+"""The pod's C host binary (kind-gpu-sim_b200/bin/gpu-probe) on a real GPU: RESULT wire
+format, known-answer lanes, exit codes.  The lanes it prints are also recomputed by the
+CPU oracle here, so the constants it embeds are checked, not trusted."""
+import os
+import re
+import subprocess
+
+import pytest
+import torch
+
+import oracle
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "kind-gpu-sim_b200", "bin", "gpu-probe")
+
+
+def run(*args, timeout=600):
+    r = subprocess.run([BIN, *args], capture_output=True, text=True, timeout=timeout)
+    results = [dict(kv.split("=", 1) for kv in line.split()[1:]) for line in r.stdout.splitlines()
+               if line.startswith("RESULT ")]
+    return r, results
+
+
+def test_one_gpu_probe_passes_with_known_answers():
+    log2n = 24
+    r, res = run("--max-gpus=1", f"--bytes={8 << log2n}", "--iters=5", "--warmup=2")
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert re.search(r"^PROBE PASS rc=0 ", r.stdout, re.M)
+    kinds = [x["kind"] for x in res]
+    assert kinds == ["init_fill", "triad", "checksum", "triad_checksum"]
+    want = oracle.stream_lanes(1 << log2n, 0)
+    for x in res:
+        assert set(x) >= {"kind", "gpus", "gpu", "bytes", "ms", "ms_med", "gbs", "frac_nominal", "frac_measured",
+                          "lanes", "match"}
+        assert float(x["ms"]) > 0 and float(x["gbs"]) > 0
+    for x in res[2:]:
+        assert x["match"] == "1"
+        assert x["lanes"] == f"{want[0]:016x},{want[1]:016x}"
+    assert int(res[1]["bytes"]) == 24 << log2n and int(res[2]["bytes"]) == 8 << log2n
+
+
+def test_size_without_known_answer_reports_na_but_still_cross_checks():
+    n = (1 << 20) + 8
+    r, res = run("--max-gpus=1", f"--bytes={8 * n}", "--iters=2", "--warmup=1", "--variant=ldg128")
+    assert r.returncode == 0, r.stdout + r.stderr
+    want = oracle.stream_lanes(n, 0)
+    assert res[2]["match"] == "na" and res[2]["lanes"] == f"{want[0]:016x},{want[1]:016x}"
+    assert res[3]["lanes"] == res[2]["lanes"]
+
+
+def test_device_count_contract():
+    have = torch.cuda.device_count()
+    r, _ = run(f"--expect-gpus={have + 1}", "--bytes=1m")
+    assert r.returncode == 3 and "PROBE FAIL rc=3" in r.stdout
+    assert "promised" in r.stderr
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_multi_gpu_probe_sharded_checksum_sweep_and_p2p():
+    have = min(torch.cuda.device_count(), 8)
+    g = 1 << (have.bit_length() - 1)  # 2, 4 or 8: n*g stays a power of two -> known answer
+    log2n = 24
+    r, res = run(f"--max-gpus={g}", f"--bytes={8 << log2n}", "--iters=5", "--warmup=2", "--sweep-max-bytes=64m",
+                 "--p2p-bytes=64m")
+    assert r.returncode == 0, r.stdout[-4000:] + r.stderr[-2000:]
+    want = oracle.stream_lanes(g << log2n, 0)
+    hexw = f"{want[0]:016x},{want[1]:016x}"
+    by = {}
+    for x in res:
+        by.setdefault(x["kind"], []).append(x)
+    assert by["checksum_sum"][0]["lanes"] == hexw and by["checksum_sum"][0]["match"] == "1"
+    combos = {x["combine"]: x for x in by["sharded_checksum"]}
+    assert set(combos) == {"nccl_allreduce_u64", "p2p_exchange_fused"}
+    for x in combos.values():
+        assert x["lanes"] == hexw and x["match"] == "1"
+    assert all(x["match"] == "1" for x in by["allreduce_check"])
+    sizes = [int(x["bytes"]) for x in by["allreduce"] if x["gpus"] == "2"]
+    assert sizes == [1 << k for k in range(10, 27)]
+    assert all(x["match"] == "1" for x in by["p2p"])
+    assert {x["mode"] for x in by["p2p"]} == {"sm_kernel", "copy_engine"}

@@ -309,7 +309,11 @@ def run_ours(args, rank, local_rank, world):
     ms_total = t_start.elapsed_time(t_end)
     triad_ms = [e[0].elapsed_time(e[1]) for e in evs]
     csum_ms = [e[1].elapsed_time(e[2]) for e in evs]
-    my_lanes = tuple(int(x) for x in (lanes if dist is None else total).cpu().numpy().view(np.uint64))
+    # this rank's own shard lanes (untimed; the exchange path only ever holds the combined ones)
+    gpuprobe.checksum_u64(a.data_ptr(), n, first, lanes.data_ptr(), ws.data_ptr(), variant, st)
+    torch.cuda.synchronize()
+    rank_lanes = tuple(int(x) for x in lanes.cpu().numpy().view(np.uint64))
+    my_lanes = rank_lanes if dist is None else tuple(int(x) for x in total.cpu().numpy().view(np.uint64))
 
     nccl_ms_step = None
     if dist is not None:
@@ -341,7 +345,7 @@ def run_ours(args, rank, local_rank, world):
     value = step_bytes / (ms_step / 1e3) / 1e9
 
     # ---- end to end: pinned host b,c -> device -> lanes back, through the pipeline ABI ----
-    e2e = None if args.no_e2e else run_e2e(args, gpuprobe, torch, b, c, n, first, my_lanes, dist, world)
+    e2e = None if args.no_e2e else run_e2e(args, gpuprobe, torch, b, c, n, first, rank_lanes, dist, world)
 
     # ---- NVLink part of the metric (N > 1): allreduce sweep, bus bandwidth ----
     nvlink = run_allreduce_sweep(args, torch, dist, world) if dist is not None else None

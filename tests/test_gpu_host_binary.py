@@ -80,3 +80,37 @@ def test_multi_gpu_probe_sharded_checksum_sweep_and_p2p():
     assert sizes == [1 << k for k in range(10, 27)]
     assert all(x["match"] == "1" for x in by["p2p"])
     assert {x["mode"] for x in by["p2p"]} == {"sm_kernel", "copy_engine"}
+
+
+def _pod(*args):
+    import json
+    import sys
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "pod_runner.py"), "--json", *args],
+                       capture_output=True, text=True, timeout=900)
+    return r, json.loads(r.stdout)
+
+
+def test_probe_pod_1gpu_runs_the_baseline_config_and_passes():
+    # BASELINE.json configs[1] exactly as the pod manifest states it: 4 GiB arrays on one GPU
+    r, out = _pod(os.path.join(ROOT, "pods", "probe-1gpu.yaml"))
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    run0 = out["runs"][0]
+    assert out["placement"] == {"nodeSelector_ok": True, "toleration_ok": True}
+    assert run0["visible"] == "0" and run0["stdout"][-1].startswith("PROBE PASS rc=0")
+    lanes = [ln for ln in run0["stdout"] if ln.startswith("RESULT kind=checksum ")][0]
+    assert "lanes=0277599ce8795db9,d761e4ba92530d51 match=1" in lanes  # golden lanes of 2^29 elements
+    assert run0["launch_to_first_result_s"] is not None
+
+
+def test_concurrent_one_gpu_pods_are_isolated():
+    # configs[3]: one 1-GPU pod per visible GPU at the same time, each seeing exactly its own device
+    g = min(torch.cuda.device_count(), 8)
+    r, out = _pod(os.path.join(ROOT, "pods", "probe-1gpu.yaml"), "--replicas", str(g), "--", "--bytes=1g", "--iters=5")
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    seen = set()
+    for k, run_k in enumerate(out["runs"]):
+        assert run_k["rc"] == 0 and run_k["visible"] == str(k)
+        info = [ln for ln in run_k["stdout"] if ln.startswith("PROBE INFO visible_gpus=")][0]
+        assert "visible_gpus=1 expect_gpus=1" in info
+        seen.add([ln for ln in run_k["stdout"] if ln.startswith("PROBE GPU index=0")][0].split("pci=")[1])
+    assert len(seen) == g  # distinct PCI bus ids: no two pods shared a GPU

@@ -212,6 +212,31 @@ def workload_config(args, world):
 
 
 # --------------------------------------------------------------------------------------
+# Sharding: pure host logic, shared by the GPU arm and the gloo CPU tests
+# --------------------------------------------------------------------------------------
+def shard_first_index(rank: int, n_per_rank: int) -> int:
+    """Rank r owns global indices [r*n, (r+1)*n) of ONE index space (weak scaling)."""
+    return rank * n_per_rank
+
+
+def to_i64(u: int) -> int:
+    """u64 bit pattern as the int64 torch/NCCL/gloo sum over (two's complement: same bits)."""
+    return u - (1 << 64) if u >= (1 << 63) else u
+
+
+def from_i64(v: int) -> int:
+    return v & ((1 << 64) - 1)
+
+
+def allreduce_lanes(dist, torch, lanes, device="cpu"):
+    """Sum (lane0, lane1) over all ranks mod 2^64 with an int64 SUM allreduce (wrapping
+    add is associative and commutative, so any backend and any order gives the same bits)."""
+    t = torch.tensor([to_i64(lanes[0]), to_i64(lanes[1])], dtype=torch.int64, device=device)
+    dist.all_reduce(t)
+    return from_i64(int(t[0].item())), from_i64(int(t[1].item()))
+
+
+# --------------------------------------------------------------------------------------
 # GPU arm
 # --------------------------------------------------------------------------------------
 def run_ours(args, rank, local_rank, world):
@@ -231,7 +256,7 @@ def run_ours(args, rank, local_rank, world):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     n = 1 << args.log2n
-    first = rank * n  # each rank owns the shard [rank*n, (rank+1)*n) of one global index space
+    first = shard_first_index(rank, n)  # each rank owns the shard [rank*n, (rank+1)*n) of one global index space
     variant = gpuprobe.VARIANTS[args.variant]
     st = torch.cuda.current_stream().cuda_stream
     b = torch.empty(n, dtype=torch.float64, device="cuda")

@@ -280,7 +280,7 @@ def run_ours(args, rank, local_rank, world):
     xchg, combine = None, "none (single GPU)"
     if dist is not None and args.combine == "exchange":
         try:
-            xchg = gpuprobe.Exchange(rank, world)
+            xchg = gpuprobe.Exchange(rank, world, 1 << args.sweep_log2max)  # payload: K4's allreduce operand
             mine = torch.tensor(list(xchg.export_handle()), dtype=torch.uint8, device="cuda")
             allh = [torch.empty_like(mine) for _ in range(world)]
             dist.all_gather(allh, mine)
@@ -373,7 +373,7 @@ def run_ours(args, rank, local_rank, world):
     e2e = None if args.no_e2e else run_e2e(args, gpuprobe, torch, b, c, n, first, rank_lanes, dist, world)
 
     # ---- NVLink part of the metric (N > 1): allreduce sweep, bus bandwidth ----
-    nvlink = run_allreduce_sweep(args, torch, dist, world) if dist is not None else None
+    nvlink = run_allreduce_sweep(args, torch, dist, world, xchg, st) if dist is not None else None
 
     if rank == 0:
         peak, peak_src = measured_peak()
@@ -484,41 +484,76 @@ def run_e2e(args, gpuprobe, torch, b, c, n, first, want_lanes, dist, world):
             "pcie_h2d_GBps": round(16 * ne / (ms / 1e3) / 1e9, 2)}
 
 
-def run_allreduce_sweep(args, torch, dist, world):
-    """In-place fp32 sum allreduce, 1 KiB .. 1 GiB per rank; busbw = algbw * 2(G-1)/G."""
+def run_allreduce_sweep(args, torch, dist, world, xchg, st):
+    """In-place fp32 sum allreduce, 1 KiB .. 1 GiB per rank; busbw = algbw * 2(G-1)/G.
+    Two implementations on the same sizes: NCCL (torch.distributed) and the probe's own
+    one-kernel allreduce over peer memory (gpu_probe_allreduce_f32, K4)."""
     rank = dist.get_rank()
     max_bytes = 1 << args.sweep_log2max
     buf = torch.ones(max_bytes // 4, dtype=torch.float32, device="cuda")
-    rows = []
-    size = 1 << 10
-    while size <= max_bytes:
-        view = buf[: size // 4]
-        iters = 20 if size >= (1 << 20) else 50
+
+    def series(fn, size, iters):
         for _ in range(5):
-            dist.all_reduce(view)
+            fn()
         torch.cuda.synchronize()
         dist.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(iters):
-            dist.all_reduce(view)
+            fn()
         e1.record()
         torch.cuda.synchronize()
         t = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
         algbw = size / (ms / 1e3) / 1e9
-        rows.append({"bytes": size, "us": round(ms * 1e3, 2), "algbw_GBps": round(algbw, 2),
-                     "busbw_GBps": round(algbw * 2 * (world - 1) / world, 2)})
+        return {"bytes": size, "us": round(ms * 1e3, 2), "algbw_GBps": round(algbw, 2),
+                "busbw_GBps": round(algbw * 2 * (world - 1) / world, 2)}
+
+    def summary(rows, what):
+        top, best = rows[-1], max(rows, key=lambda r: r["busbw_GBps"])
+        return {"collective": what, "busbw_GBps_at_max": top["busbw_GBps"], "max_bytes": top["bytes"],
+                "busbw_GBps_peak": best["busbw_GBps"], "peak_bytes": best["bytes"],
+                "frac_of_nominal_900": round(top["busbw_GBps"] / NVLINK_NOMINAL_GBS, 4),
+                "latency_us_1KiB": rows[0]["us"], "sweep": rows}
+
+    rows_nccl, rows_own = [], []
+    size = 1 << 10
+    while size <= max_bytes:
+        view = buf[: size // 4]
+        iters = 20 if size >= (1 << 20) else 50
+        rows_nccl.append(series(lambda: dist.all_reduce(view), size, iters))
         buf.fill_(1.0)
+        if xchg is not None:
+            rows_own.append(series(lambda: xchg.allreduce_f32(0, size // 4, 0, st), size, iters))
         size <<= 1
-    top = rows[-1]
-    best = max(rows, key=lambda r: r["busbw_GBps"])
-    return {"collective": "NCCL allreduce fp32 sum in place (torch.distributed), max over ranks",
-            "busbw_GBps_at_max": top["busbw_GBps"], "max_bytes": top["bytes"],
-            "busbw_GBps_peak": best["busbw_GBps"], "peak_bytes": best["bytes"],
-            "frac_of_nominal_900": round(top["busbw_GBps"] / NVLINK_NOMINAL_GBS, 4),
-            "latency_us_1KiB": rows[0]["us"], "sweep": rows} if rank == 0 else None
+    own = None
+    if xchg is not None:
+        # correctness of K4 at the bench's scale: integer-valued inputs, closed-form sum, every rank
+        import gpuprobe
+        n_chk = min(max_bytes // 4, (1 << 22) + 3)
+        src = (torch.arange(n_chk, device="cuda", dtype=torch.float32) % 7 + 1) * float(rank + 1)
+        gpuprobe.p2p_copy(xchg.buffer, src.data_ptr(), 4 * n_chk, st)
+        torch.cuda.synchronize()
+        dist.barrier()
+        xchg.allreduce_f32(0, n_chk, 0, st)
+        out = torch.empty_like(src)
+        gpuprobe.p2p_copy(out.data_ptr(), xchg.buffer, 4 * n_chk, st)
+        torch.cuda.synchronize()
+        want = (torch.arange(n_chk, device="cuda", dtype=torch.float32) % 7 + 1) * float(world * (world + 1) // 2)
+        ok = torch.tensor([int(torch.equal(out, want) and xchg.status() == 0)], dtype=torch.int32, device="cuda")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) != 1:
+            raise SystemExit(f"bench.py: rank {rank}: gpu_probe_allreduce_f32 result differs from the closed-form sum")
+        own = summary(rows_own, "gpu_probe_allreduce_f32 (K4: one kernel, pull-reduce + push-broadcast over NVLink peer "
+                                "memory), max over ranks")
+        own["checked"] = f"{n_chk} elements against the closed-form sum on every rank"
+    if rank != 0:
+        return None
+    out = summary(rows_nccl, "NCCL allreduce fp32 sum in place (torch.distributed), max over ranks")
+    if own is not None:
+        out["p2p_kernel"] = own
+    return out
 
 
 def main():

@@ -134,9 +134,10 @@ int gpu_probe_p2p_copy(void *dst, const void *src, uint64_t bytes, void *stream)
  * own mailbox and writes the global sum to out_lanes -- every rank ends with the same
  * two words, bit-identical to a single-GPU checksum of the whole buffer.
  *
- * A gpu_probe_exchange is one rank's mailbox (1280 bytes of device memory) plus the
- * addresses of the peers' mailboxes.
- *   create          [blocking, ALLOCATES] on the current device.
+ * A gpu_probe_exchange is one rank's symmetric segment -- a 256 KiB header (lanes mailbox,
+ * barrier flags) plus an optional data buffer of `buffer_bytes` (the allreduce operand) --
+ * and the addresses of the peers' segments.
+ *   create          [blocking, ALLOCATES 256 KiB + buffer_bytes] on the current device.
  *   connect_local   ranks living in one process: enables peer access both ways and
  *                   hands raw pointers around.  xs[r] must be rank r.
  *   export / connect_ipc   one process per GPU: export gives this rank's CUDA IPC
@@ -152,7 +153,8 @@ typedef struct gpu_probe_exchange gpu_probe_exchange;
 #define GPU_PROBE_EXCHANGE_MAX_RANKS 16
 #define GPU_PROBE_EXCHANGE_HANDLE_BYTES 64
 
-int gpu_probe_exchange_create(gpu_probe_exchange **out, int rank, int world);
+int gpu_probe_exchange_create(gpu_probe_exchange **out, int rank, int world,
+                              uint64_t buffer_bytes);
 int gpu_probe_exchange_connect_local(gpu_probe_exchange *const *xs, int world);
 int gpu_probe_exchange_export(gpu_probe_exchange *x,
                               unsigned char handle[GPU_PROBE_EXCHANGE_HANDLE_BYTES]);
@@ -160,6 +162,20 @@ int gpu_probe_exchange_connect_ipc(gpu_probe_exchange *x, const unsigned char *h
 int gpu_probe_exchange_set_timeout_ms(gpu_probe_exchange *x, uint64_t ms);
 int gpu_probe_exchange_status(gpu_probe_exchange *x);
 int gpu_probe_exchange_destroy(gpu_probe_exchange *x);
+
+/* This rank's data buffer inside the segment (device pointer; NULL when buffer_bytes was 0). */
+void *gpu_probe_exchange_buffer(gpu_probe_exchange *x);
+uint64_t gpu_probe_exchange_buffer_bytes(gpu_probe_exchange *x);
+
+/* K4  in-place fp32 sum allreduce of `count` elements at buffer + offset_bytes (16-byte
+ * aligned offset) over all ranks, in ONE kernel over NVLink peer memory: rank r pulls its
+ * slice from every rank, adds in rank order 0..G-1 and pushes the sums back to every rank.
+ * All ranks end with bit-identical data.  `ctas` = 0 lets the library size the grid (every
+ * rank must pass the same count and ctas).  World sizes 1..8.  This is the probe's own
+ * collective, timed beside NCCL's allreduce (SURVEY 8d "Allreduce sweep"); same rules as the
+ * *_exchange calls above. */
+int gpu_probe_allreduce_f32(gpu_probe_exchange *x, uint64_t offset_bytes, uint64_t count,
+                            int ctas, void *stream);
 
 /* K2 + lanes exchange in one launch.  Arguments as gpu_probe_checksum_u64; out_lanes
  * receives the sum over ALL ranks.  Must be called with x's device current. */

@@ -1,0 +1,199 @@
+// probe_allreduce.cu -- K4: fp32 sum allreduce over NVLink peer memory, one kernel.
+//
+// The NVLink half of the headline metric is an allreduce sweep (SURVEY.md section 8d,
+// "Allreduce sweep").  NCCL is the baseline the host binary and bench.py time; this is
+// the probe's own collective, written against the same symmetric segments the lanes
+// exchange uses (probe_exchange.cu), so it needs no NCCL and no extra launches:
+//
+//   rank r owns slice r of the buffer.  For every 16-byte vector of its slice it PULLS the
+//   vector from all G buffers (its own + G-1 peers over NVLink), adds them in rank order,
+//   and PUSHES the sum back into all G buffers at the same offset.  The thread that
+//   overwrites an element is the only one that ever reads it, so the reduce-scatter and
+//   the all-gather need no barrier between them: one barrier before (every input is
+//   ready) and one after (every push has landed) is all the synchronisation there is.
+//
+// Per direction each GPU moves 2(G-1)/G x bytes, so bus bandwidth = algbw x 2(G-1)/G is
+// bounded by the NVLink rate (900 GB/s per direction nominal).  Every element is summed by
+// exactly one rank in a fixed order, so all ranks end with bit-identical results.
+// Barriers are per CTA: CTA b of every rank works on the same vectors of every slice, so it
+// only has to meet CTA b of the peers (flags[b][rank] in the segment header) -- no
+// grid-wide synchronisation, no co-residency requirement beyond "peer CTA b gets to run".
+// No reference counterpart (slot: /root/reference/pods/nvidia-gpu-test-pod.yaml:9).
+#include "gpu_probe.h"
+
+#include <cstring>
+#include <cuda_runtime.h>
+
+#include "probe_common.cuh"
+#include "probe_exchange.h"
+
+namespace probe {
+
+constexpr int kArThreads = 512;
+
+struct AllreduceArgs {
+  unsigned char *seg[kMaxRanks];  // segment base of rank p as THIS GPU addresses it
+  int rank, world;
+  unsigned long long timeout_ns;
+  uint64_t offset_bytes;  // operand = payload + offset_bytes
+  uint64_t count;         // fp32 elements
+};
+
+__device__ __forceinline__ float4 ld_peer(const float4 *p) {  // system-coherent, never from a stale L1 line
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_peer(float4 *p, const float4 &v) {
+  asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+               :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float ld_peer(const float *p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_peer(float *p, float v) {
+  asm volatile("st.relaxed.sys.global.f32 [%0], %1;" :: "l"(p), "f"(v) : "memory");
+}
+
+// CTA b of this rank meets CTA b of every peer.  Returns false on timeout.
+// Release/acquire at system scope on the flag; the __syncthreads on either side extend
+// that ordering to every thread of the CTA (cumulativity).
+__device__ __forceinline__ bool cta_barrier(const AllreduceArgs &a, uint64_t epoch) {
+  __shared__ int timed_out;
+  if (threadIdx.x == 0) timed_out = 0;
+  __syncthreads();
+  if (threadIdx.x < a.world) {
+    const int p = threadIdx.x;
+    uint64_t *theirs = reinterpret_cast<uint64_t *>(a.seg[p]) + kFlagsOffsetWords + size_t(blockIdx.x) * kMaxRanks + a.rank;
+    __threadfence_system();
+    st_release_sys(theirs, epoch);
+    const uint64_t *mine = reinterpret_cast<const uint64_t *>(a.seg[a.rank]) + kFlagsOffsetWords +
+                           size_t(blockIdx.x) * kMaxRanks + p;
+    const unsigned long long t0 = global_ns();
+    while (ld_acquire_sys(mine) < epoch) {
+      if (global_ns() - t0 > a.timeout_ns) { timed_out = 1; break; }
+    }
+  }
+  __syncthreads();
+  return timed_out == 0;
+}
+
+template <int G, int U>
+__device__ __forceinline__ void reduce_broadcast(const AllreduceArgs &a, uint64_t v_lo, uint64_t v_hi) {
+  // vectors [v_lo, v_hi) of the operand belong to this rank; CTAs stride over them
+  float4 *buf[G];
+#pragma unroll
+  for (int p = 0; p < G; ++p) buf[p] = reinterpret_cast<float4 *>(a.seg[p] + kPayloadOffsetBytes + a.offset_bytes);
+  const uint64_t tile = uint64_t(kArThreads) * U;
+  for (uint64_t base = v_lo + blockIdx.x * tile; base < v_hi; base += uint64_t(gridDim.x) * tile) {
+    float4 v[U][G];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint64_t i = base + uint64_t(u) * kArThreads + threadIdx.x;
+      if (i < v_hi) {
+#pragma unroll
+        for (int p = 0; p < G; ++p) v[u][p] = ld_peer(buf[p] + i);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint64_t i = base + uint64_t(u) * kArThreads + threadIdx.x;
+      if (i < v_hi) {
+        float4 s = v[u][0];
+#pragma unroll
+        for (int p = 1; p < G; ++p) {  // fixed order 0,1,..,G-1: the defined result
+          s.x += v[u][p].x; s.y += v[u][p].y; s.z += v[u][p].z; s.w += v[u][p].w;
+        }
+#pragma unroll
+        for (int p = 0; p < G; ++p) st_peer(buf[p] + i, s);
+      }
+    }
+  }
+}
+
+template <int G, int U>
+__global__ void __launch_bounds__(kArThreads)
+allreduce_f32_kernel(const AllreduceArgs a) {
+  uint64_t *hdr = reinterpret_cast<uint64_t *>(a.seg[a.rank]);
+  __shared__ uint64_t epoch0;
+  if (threadIdx.x == 0) epoch0 = hdr[kCtaEpochOffsetWords + blockIdx.x];
+  __syncthreads();
+  const uint64_t e = epoch0;
+  bool ok = cta_barrier(a, e + 1);  // every rank's operand is ready to be read
+  if (ok) {
+    const uint64_t nvec = a.count / 4;
+    const uint64_t v_lo = nvec * uint64_t(a.rank) / G, v_hi = nvec * uint64_t(a.rank + 1) / G;
+    reduce_broadcast<G, U>(a, v_lo, v_hi);
+    // fewer than 4 trailing elements: the last rank owns them
+    if (a.rank == G - 1 && blockIdx.x == 0 && threadIdx.x < (a.count & 3)) {
+      const uint64_t i = nvec * 4 + threadIdx.x;
+      float s = 0.f;
+#pragma unroll
+      for (int p = 0; p < G; ++p) {
+        const float x = ld_peer(reinterpret_cast<const float *>(a.seg[p] + kPayloadOffsetBytes + a.offset_bytes) + i);
+        s = p == 0 ? x : s + x;
+      }
+#pragma unroll
+      for (int p = 0; p < G; ++p) st_peer(reinterpret_cast<float *>(a.seg[p] + kPayloadOffsetBytes + a.offset_bytes) + i, s);
+    }
+    ok = cta_barrier(a, e + 2);  // every push has landed everywhere before any rank's kernel ends
+  }
+  if (threadIdx.x == 0) {
+    hdr[kCtaEpochOffsetWords + blockIdx.x] = e + 2;
+    if (!ok) hdr[1] = 1;  // sticky error flag, read by gpu_probe_exchange_status
+  }
+}
+
+template <int G>
+static int launch_allreduce(const AllreduceArgs &a, unsigned grid, cudaStream_t st) {
+  constexpr int U = G <= 2 ? 8 : (G <= 4 ? 4 : 2);  // G*U 16-byte loads in flight per thread
+  allreduce_f32_kernel<G, U><<<grid, kArThreads, 0, st>>>(a);
+  return int(cudaGetLastError());
+}
+
+}  // namespace probe
+
+using namespace probe;
+
+extern "C" int gpu_probe_allreduce_f32(gpu_probe_exchange *x, uint64_t offset_bytes, uint64_t count, int ctas,
+                                       void *stream) {
+  if (!live(x) || !x->connected) return GPU_PROBE_ENOTREADY;
+  if (x->buffer_bytes == 0 || (offset_bytes & 15)) return GPU_PROBE_EINVAL;
+  if (offset_bytes > x->buffer_bytes || count > (x->buffer_bytes - offset_bytes) / 4) return GPU_PROBE_ETOOBIG;
+  if (ctas < 0 || ctas > kMaxCommCtas) return GPU_PROBE_EINVAL;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return int(e);
+  if (dev != x->device) return GPU_PROBE_EINVAL;
+  if (count == 0) return 0;  // every rank passes the same count, so every rank skips
+  AllreduceArgs a;
+  std::memset(&a, 0, sizeof(a));
+  for (int p = 0; p < x->world; ++p) a.seg[p] = reinterpret_cast<unsigned char *>(x->peer[p]);
+  a.rank = x->rank; a.world = x->world; a.timeout_ns = x->timeout_ns;
+  a.offset_bytes = offset_bytes; a.count = count;
+  // Grid: a function of (count, world, SM count) only, so every rank picks the same one --
+  // CTA b must exist on every rank.  All CTAs are co-resident (<= 1 per SM).
+  int sms = 0;
+  e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (e != cudaSuccess) return int(e);
+  const uint64_t slice_vecs = (count / 4 + x->world - 1) / x->world;
+  uint64_t want = (slice_vecs + kArThreads - 1) / kArThreads;  // at least one vector per thread
+  if (want < 1) want = 1;
+  unsigned grid = ctas > 0 ? unsigned(ctas) : unsigned(want < uint64_t(sms) ? want : uint64_t(sms));
+  if (grid > unsigned(sms)) grid = unsigned(sms);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (x->world) {
+    case 1: return launch_allreduce<1>(a, grid, st);
+    case 2: return launch_allreduce<2>(a, grid, st);
+    case 3: return launch_allreduce<3>(a, grid, st);
+    case 4: return launch_allreduce<4>(a, grid, st);
+    case 5: return launch_allreduce<5>(a, grid, st);
+    case 6: return launch_allreduce<6>(a, grid, st);
+    case 7: return launch_allreduce<7>(a, grid, st);
+    case 8: return launch_allreduce<8>(a, grid, st);
+    default: return GPU_PROBE_EINVAL;  // more than 8 ranks: not one NVSwitch domain of this probe
+  }
+}

@@ -119,20 +119,31 @@ constexpr size_t kWorkspaceBytes =
 // on every peer (NVLink P2P stores), then waits for the peers' slots in its OWN mailbox
 // and adds them.  Wrapping u64 sums commute, so arrival order cannot change a bit.
 //
-// Mailbox layout (one per GPU, uint64 words; allocated by gpu_probe_exchange_create):
-//   word 0         : call counter of this GPU (local only)
-//   word 1         : sticky error flag (local only; 1 = a peer never arrived)
-//   words 32 ..    : slots[2][kMaxRanks] of {lane0, lane1, epoch, pad}; the buffer is
-//                    chosen by epoch parity.  Two buffers suffice: a rank can only
-//                    start call k+2 after every peer has written call k+1, which each
-//                    peer does after it finished reading call k.
+// Segment layout (one per GPU, allocated by gpu_probe_exchange_create; byte offsets):
+//   0      mailbox   word 0: call counter of this GPU (local only)
+//                    word 1: sticky error flag (local only; 1 = a peer never arrived)
+//                    words 32..: slots[2][kMaxRanks] of {lane0, lane1, epoch, pad}; the buffer
+//                    is chosen by epoch parity.  Two buffers suffice: a rank can only start
+//                    call k+2 after every peer has written call k+1, which each peer does
+//                    after it finished reading call k.
+//   8 KiB  cta_epoch[kMaxCommCtas]            barrier epoch of CTA b on this GPU (local only)
+//   16 KiB flags[kMaxCommCtas][kMaxRanks]     flags[b][p] = last barrier epoch CTA b of rank p
+//                                             signalled to this GPU (written by p, polled here)
+//   256 KiB payload                           the symmetric data buffer (allreduce operand)
 constexpr int kMaxRanks = 16;
 constexpr int kSlotWords = 4;
 constexpr int kMailboxSlotsOffsetWords = 32;
 constexpr size_t kMailboxBytes = sizeof(uint64_t) * (kMailboxSlotsOffsetWords + 2 * kMaxRanks * kSlotWords);
+constexpr int kMaxCommCtas = 1024;
+constexpr size_t kCtaEpochOffsetWords = 8192 / 8;
+constexpr size_t kFlagsOffsetWords = 16384 / 8;
+constexpr size_t kPayloadOffsetBytes = 256 * 1024;
+static_assert(kMailboxBytes <= 8192, "mailbox overlaps the epoch table");
+static_assert(kCtaEpochOffsetWords + kMaxCommCtas <= kFlagsOffsetWords, "epoch table overlaps the flags");
+static_assert((kFlagsOffsetWords + size_t(kMaxCommCtas) * kMaxRanks) * 8 <= kPayloadOffsetBytes, "flags overlap the payload");
 
 struct ExchangeArgs {           // passed to kernels by value; world == 0: no exchange
-  uint64_t *mailbox[kMaxRanks]; // mailbox[p]: rank p's mailbox as THIS GPU addresses it
+  uint64_t *mailbox[kMaxRanks]; // mailbox[p]: rank p's segment base as THIS GPU addresses it
   int rank, world;
   unsigned long long timeout_ns;
 };

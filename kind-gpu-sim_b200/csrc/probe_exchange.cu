@@ -23,6 +23,7 @@
 #include <new>
 
 #include "probe_common.cuh"
+#include "probe_exchange.h"
 #include "probe_launch.h"
 
 using namespace probe;
@@ -30,31 +31,13 @@ using namespace probe;
 static_assert(GPU_PROBE_EXCHANGE_MAX_RANKS == kMaxRanks, "header and device code disagree on the rank limit");
 static_assert(GPU_PROBE_EXCHANGE_HANDLE_BYTES == sizeof(cudaIpcMemHandle_t), "IPC handle size");
 
-struct gpu_probe_exchange {
-  uint32_t magic;
-  int device, rank, world;
-  bool connected;
-  uint64_t *mailbox;            // this rank's mailbox (cudaMalloc on `device`)
-  uint64_t *peer[kMaxRanks];    // every rank's mailbox as addressed from `device`
-  bool ipc_opened[kMaxRanks];   // peer[p] came from cudaIpcOpenMemHandle
-  unsigned long long timeout_ns;
-};
 
-static constexpr uint32_t kXMagic = 0x58434847u;  // "XCHG"
-static inline bool live(const gpu_probe_exchange *x) { return x && x->magic == kXMagic; }
-
-namespace {
-struct DeviceGuard {  // run a few calls with another device current, then put the old one back
-  int prev = -1;
-  explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
-  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
-};
-}  // namespace
-
-extern "C" int gpu_probe_exchange_create(gpu_probe_exchange **out, int rank, int world) {
+extern "C" int gpu_probe_exchange_create(gpu_probe_exchange **out, int rank, int world, uint64_t buffer_bytes) {
   if (!out) return GPU_PROBE_EINVAL;
   *out = nullptr;
   if (world < 1 || world > kMaxRanks || rank < 0 || rank >= world) return GPU_PROBE_EINVAL;
+  if (buffer_bytes > (1ull << 36)) return GPU_PROBE_ETOOBIG;
+  buffer_bytes = (buffer_bytes + 255) & ~uint64_t(255);
   int dev = -1;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return int(e);
@@ -62,8 +45,10 @@ extern "C" int gpu_probe_exchange_create(gpu_probe_exchange **out, int rank, int
   if (!x) return int(cudaErrorMemoryAllocation);
   x->device = dev; x->rank = rank; x->world = world;
   x->timeout_ns = 10ull * 1000 * 1000 * 1000;  // a peer that is 10 s late is not coming
-  e = cudaMalloc(reinterpret_cast<void **>(&x->mailbox), kMailboxBytes);
-  if (e == cudaSuccess) e = cudaMemset(x->mailbox, 0, kMailboxBytes);
+  x->buffer_bytes = buffer_bytes;
+  // header (mailbox, barrier epochs and flags) and payload are ONE allocation: one IPC handle maps both
+  e = cudaMalloc(reinterpret_cast<void **>(&x->mailbox), kPayloadOffsetBytes + buffer_bytes);
+  if (e == cudaSuccess) e = cudaMemset(x->mailbox, 0, kPayloadOffsetBytes);
   if (e == cudaSuccess) e = cudaDeviceSynchronize();  // zeroed before any peer can learn the address
   if (e != cudaSuccess) {
     if (x->mailbox) cudaFree(x->mailbox);
@@ -160,6 +145,13 @@ extern "C" int gpu_probe_exchange_destroy(gpu_probe_exchange *x) {
   delete x;
   return 0;
 }
+
+extern "C" void *gpu_probe_exchange_buffer(gpu_probe_exchange *x) {
+  if (!live(x) || x->buffer_bytes == 0) return nullptr;
+  return reinterpret_cast<unsigned char *>(x->mailbox) + kPayloadOffsetBytes;
+}
+
+extern "C" uint64_t gpu_probe_exchange_buffer_bytes(gpu_probe_exchange *x) { return live(x) ? x->buffer_bytes : 0; }
 
 static int exchange_args(const gpu_probe_exchange *x, ExchangeArgs *a) {
   if (!live(x) || !x->connected) return GPU_PROBE_ENOTREADY;

@@ -63,7 +63,13 @@ def lib() -> ctypes.CDLL:
         L.gpu_probe_pipeline_run_host.argtypes = [_vp, _vp, _vp, _vp, ctypes.c_double, _u64, _u64,
                                                   ctypes.POINTER(_u64)]
         L.gpu_probe_pipeline_destroy.argtypes = [_vp]
-        L.gpu_probe_exchange_create.argtypes = [ctypes.POINTER(_vp), ctypes.c_int, ctypes.c_int]
+        L.gpu_probe_exchange_create.argtypes = [ctypes.POINTER(_vp), ctypes.c_int, ctypes.c_int, _u64]
+        L.gpu_probe_exchange_buffer.argtypes = [_vp]
+        L.gpu_probe_exchange_buffer.restype = _vp
+        L.gpu_probe_exchange_buffer_bytes.argtypes = [_vp]
+        L.gpu_probe_exchange_buffer_bytes.restype = _u64
+        L.gpu_probe_allreduce_f32.argtypes = [_vp, _u64, _u64, ctypes.c_int, _vp]
+        L.gpu_probe_allreduce_f32.restype = ctypes.c_int
         L.gpu_probe_exchange_connect_local.argtypes = [ctypes.POINTER(_vp), ctypes.c_int]
         L.gpu_probe_exchange_export.argtypes = [_vp, ctypes.c_char_p]
         L.gpu_probe_exchange_connect_ipc.argtypes = [_vp, ctypes.c_char_p]
@@ -171,10 +177,23 @@ class Exchange:
     Create with the rank's device current; then either Exchange.connect_local([...]) for
     ranks in one process, or export_handle() / connect_ipc(all_handles) across processes."""
 
-    def __init__(self, rank: int, world: int):
+    def __init__(self, rank: int, world: int, buffer_bytes: int = 0):
         self._h = _vp()
         self.rank, self.world = rank, world
-        _check(lib().gpu_probe_exchange_create(ctypes.byref(self._h), rank, world), "gpu_probe_exchange_create")
+        _check(lib().gpu_probe_exchange_create(ctypes.byref(self._h), rank, world, buffer_bytes),
+               "gpu_probe_exchange_create")
+
+    @property
+    def buffer(self) -> int:
+        """Device address of this rank's data buffer inside the segment (0 if none)."""
+        return int(lib().gpu_probe_exchange_buffer(self._h) or 0)
+
+    @property
+    def buffer_bytes(self) -> int:
+        return int(lib().gpu_probe_exchange_buffer_bytes(self._h))
+
+    def allreduce_f32(self, offset_bytes: int, count: int, ctas: int = 0, stream: int = 0) -> None:
+        _check(lib().gpu_probe_allreduce_f32(self._h, offset_bytes, count, ctas, stream), "gpu_probe_allreduce_f32")
 
     @staticmethod
     def connect_local(xs: "list[Exchange]") -> None:

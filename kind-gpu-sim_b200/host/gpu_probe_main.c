@@ -11,8 +11,9 @@
  *      against the roofline, lanes against the known answers (golden_lanes.h);
  *   3. N > 1: the sharded checksum combined over GPUs, two ways -- K2 followed by an NCCL
  *      u64 allreduce, and the one-kernel checksum+exchange over peer memory;
- *   4. N > 1: NCCL fp32 allreduce sweep 1 KiB..1 GiB at 2/4/8 GPUs (bus GB/s against
- *      900 GB/s per direction) and P2P copies GPU0 -> GPUk (SM copy kernel and copy engine).
+ *   4. N > 1: fp32 allreduce sweep 1 KiB..1 GiB at 2/4/8 GPUs (bus GB/s against 900 GB/s per
+ *      direction), NCCL and the probe's own one-kernel allreduce side by side, and P2P
+ *      copies GPU0 -> GPUk (SM copy kernel and copy engine).
  *
  * Everything numeric goes through the C ABI in include/gpu_probe.h (libgpuprobe.so,
  * hand-written sm_100a kernels).  There is no CPU path in this program: the expected
@@ -453,93 +454,137 @@ static int phase_sharded(const options *o, gpu_state *gs, int ng, uint64_t n, nc
   return 0;
 }
 
-/* --------------------------------- phase C: NCCL allreduce sweep at 2/4/8 GPUs */
-static int phase_sweep(const options *o, gpu_state *gs, int ng, nccl_api *nc) {
+/* ------------- phase C: allreduce sweep at 2/4/8 GPUs -- NCCL and the probe's own K4 */
+/* One timed series: `iters` back-to-back in-place allreduces of S bytes on every GPU of the
+ * group, bracketed by events on each GPU's stream; per-iteration time = slowest GPU. */
+static int time_allreduce(int use_nccl, nccl_api *nc, ncclComm_t *comms, gpu_state *gs, gpu_probe_exchange **xs,
+                          float **bufs, int G, uint64_t S, int iters, double *ms_out) {
   int rc;
-  const int group_sizes[] = {2, 4, 8, 16};
-  for (int gi = 0; gi < 4; ++gi) {
-    const int G = group_sizes[gi];
-    if (G > ng) break;
-    ncclComm_t comms[MAX_GPUS];
-    int devs[MAX_GPUS];
-    for (int d = 0; d < G; ++d) devs[d] = gs[d].dev;
-    NC(nc, nc->CommInitAll(comms, G, devs));
-    /* the sweep runs in place on a[] viewed as fp32 (phase A/B are done with it) */
-    uint64_t max_bytes = o->sweep_max_bytes;
-    if (max_bytes > o->bytes) { /* a[] is smaller than the sweep: largest power of two that fits */
-      max_bytes = 1024;
-      while (max_bytes * 2 <= o->bytes) max_bytes *= 2;
-    }
-    /* correctness first: integer-valued floats, closed-form sum */
-    {
-      enum { CHECK_ELEMS = 1 << 18 };
-      float *h = (float *)malloc(sizeof(float) * CHECK_ELEMS);
-      if (!h) return RC_CUDA;
-      const uint64_t celems = (max_bytes / 4 < CHECK_ELEMS) ? max_bytes / 4 : CHECK_ELEMS;
+  for (int i = -5; i < iters; ++i) {
+    if (i == 0)
       for (int d = 0; d < G; ++d) {
-        for (uint64_t i = 0; i < celems; ++i) h[i] = (float)((d + 1) * (int)(1 + (i % 7)));
         CU(cudaSetDevice(gs[d].dev));
-        CU(cudaMemcpyAsync(gs[d].a, h, 4 * celems, cudaMemcpyHostToDevice, gs[d].st));
-        CU(cudaStreamSynchronize(gs[d].st));
+        CU(cudaEventRecord(gs[d].ev[0], gs[d].st));
       }
+    if (use_nccl) {
       NC(nc, nc->GroupStart());
       for (int d = 0; d < G; ++d)
-        NC(nc, nc->AllReduce(gs[d].a, gs[d].a, celems, ncclFloat, ncclSum, comms[d], gs[d].st));
+        NC(nc, nc->AllReduce(bufs[d], bufs[d], S / 4, ncclFloat, ncclSum, comms[d], gs[d].st));
       NC(nc, nc->GroupEnd());
-      if ((rc = sync_all(gs, G))) return rc;
-      int ok = 1;
-      for (int d = 0; d < G && ok; ++d) {
+    } else {
+      for (int d = 0; d < G; ++d) {
         CU(cudaSetDevice(gs[d].dev));
-        CU(cudaMemcpy(h, gs[d].a, 4 * celems, cudaMemcpyDeviceToHost));
-        for (uint64_t i = 0; i < celems; ++i)
-          if (h[i] != (float)((G * (G + 1) / 2) * (int)(1 + (i % 7)))) { ok = 0; break; }
+        PR(gpu_probe_allreduce_f32(xs[d], 0, S / 4, 0, gs[d].st));
       }
-      free(h);
-      printf("RESULT kind=allreduce_check gpus=%d gpu=all bytes=%" PRIu64 " ms=na ms_med=na gbs=na frac_nominal=na "
-             "frac_measured=na lanes=na match=%d\n", G, 4 * celems, ok);
-      if (!ok) fail(RC_PARITY);
     }
-    for (int d = 0; d < G; ++d) { /* zeros: sums stay finite however often the prefix is reduced */
+  }
+  for (int d = 0; d < G; ++d) {
+    CU(cudaSetDevice(gs[d].dev));
+    CU(cudaEventRecord(gs[d].ev[1], gs[d].st));
+  }
+  if ((rc = sync_all(gs, G))) return rc;
+  double ms = 0;
+  for (int d = 0; d < G; ++d) {
+    float t;
+    CU(cudaSetDevice(gs[d].dev));
+    CU(cudaEventElapsedTime(&t, gs[d].ev[0], gs[d].ev[1]));
+    if (t / iters > ms) ms = t / iters;
+  }
+  *ms_out = ms;
+  return 0;
+}
+
+/* Integer-valued floats in, closed-form sum out: exact in fp32 whatever the reduction order. */
+static int check_allreduce(int use_nccl, nccl_api *nc, ncclComm_t *comms, gpu_state *gs, gpu_probe_exchange **xs,
+                           float **bufs, int G, uint64_t max_bytes, int *ok_out) {
+  enum { CHECK_ELEMS = (1 << 18) + 3 };
+  int rc;
+  float *h = (float *)malloc(sizeof(float) * CHECK_ELEMS);
+  if (!h) return RC_CUDA;
+  const uint64_t celems = (max_bytes / 4 < CHECK_ELEMS) ? max_bytes / 4 : CHECK_ELEMS;
+  for (int d = 0; d < G; ++d) {
+    for (uint64_t i = 0; i < celems; ++i) h[i] = (float)((d + 1) * (int)(1 + (i % 7)));
+    CU(cudaSetDevice(gs[d].dev));
+    CU(cudaMemcpyAsync(bufs[d], h, 4 * celems, cudaMemcpyHostToDevice, gs[d].st));
+    CU(cudaStreamSynchronize(gs[d].st));
+  }
+  if (use_nccl) {
+    NC(nc, nc->GroupStart());
+    for (int d = 0; d < G; ++d)
+      NC(nc, nc->AllReduce(bufs[d], bufs[d], celems, ncclFloat, ncclSum, comms[d], gs[d].st));
+    NC(nc, nc->GroupEnd());
+  } else {
+    for (int d = 0; d < G; ++d) {
       CU(cudaSetDevice(gs[d].dev));
-      CU(cudaMemsetAsync(gs[d].a, 0, max_bytes, gs[d].st));
+      PR(gpu_probe_allreduce_f32(xs[d], 0, celems, 0, gs[d].st));
     }
-    double best_bus = 0;
-    uint64_t best_bytes = 0;
-    for (uint64_t S = 1024; S <= max_bytes; S <<= 1) {
-      const int iters = S >= (1u << 20) ? o->iters : 2 * o->iters;
-      for (int i = -5; i < iters; ++i) {
-        if (i == 0)
-          for (int d = 0; d < G; ++d) {
-            CU(cudaSetDevice(gs[d].dev));
-            CU(cudaEventRecord(gs[d].ev[0], gs[d].st));
-          }
-        NC(nc, nc->GroupStart());
-        for (int d = 0; d < G; ++d)
-          NC(nc, nc->AllReduce(gs[d].a, gs[d].a, S / 4, ncclFloat, ncclSum, comms[d], gs[d].st));
-        NC(nc, nc->GroupEnd());
-      }
-      for (int d = 0; d < G; ++d) {
-        CU(cudaSetDevice(gs[d].dev));
-        CU(cudaEventRecord(gs[d].ev[1], gs[d].st));
-      }
-      if ((rc = sync_all(gs, G))) return rc;
-      double ms = 0;
-      for (int d = 0; d < G; ++d) {
-        float t;
-        CU(cudaSetDevice(gs[d].dev));
-        CU(cudaEventElapsedTime(&t, gs[d].ev[0], gs[d].ev[1]));
-        if (t / iters > ms) ms = t / iters;
-      }
-      const double algbw = (double)S / (ms * 1e-3) / 1e9;
-      const double busbw = algbw * 2.0 * (G - 1) / G;
-      if (busbw > best_bus) { best_bus = busbw; best_bytes = S; }
-      printf("RESULT kind=allreduce gpus=%d gpu=all bytes=%" PRIu64 " ms=%.5f ms_med=%.5f gbs=%.2f frac_nominal=%.4f "
-             "frac_measured=na lanes=na match=na us=%.2f algbw=%.2f busbw=%.2f\n",
-             G, S, ms, ms, busbw, busbw / NOMINAL_NVLINK_GBS, ms * 1e3, algbw, busbw);
+  }
+  if ((rc = sync_all(gs, G))) return rc;
+  int ok = 1;
+  for (int d = 0; d < G && ok; ++d) {
+    CU(cudaSetDevice(gs[d].dev));
+    CU(cudaMemcpy(h, bufs[d], 4 * celems, cudaMemcpyDeviceToHost));
+    for (uint64_t i = 0; i < celems; ++i)
+      if (h[i] != (float)((G * (G + 1) / 2) * (int)(1 + (i % 7)))) { ok = 0; break; }
+    if (!use_nccl && gpu_probe_exchange_status(xs[d]) != 0) ok = 0;
+  }
+  free(h);
+  printf("RESULT kind=allreduce_check gpus=%d gpu=all bytes=%" PRIu64 " ms=na ms_med=na gbs=na frac_nominal=na "
+         "frac_measured=na lanes=na match=%d impl=%s\n", G, 4 * celems, ok, use_nccl ? "nccl" : "p2p_kernel");
+  if (!ok) fail(RC_PARITY);
+  *ok_out = ok;
+  return 0;
+}
+
+static int phase_sweep(const options *o, gpu_state *gs, int ng, nccl_api *nc) {
+  int rc;
+  const int group_sizes[] = {2, 4, 8};
+  for (int gi = 0; gi < 3; ++gi) {
+    const int G = group_sizes[gi];
+    if (G > ng) break;
+    /* operands live in symmetric segments (one per GPU of the group): both NCCL and K4 reduce them in place */
+    gpu_probe_exchange *xs[MAX_GPUS];
+    float *bufs[MAX_GPUS];
+    ncclComm_t comms[MAX_GPUS];
+    int devs[MAX_GPUS];
+    const uint64_t max_bytes = o->sweep_max_bytes;
+    for (int d = 0; d < G; ++d) {
+      devs[d] = gs[d].dev;
+      CU(cudaSetDevice(gs[d].dev));
+      PR(gpu_probe_exchange_create(&xs[d], d, G, max_bytes));
+      bufs[d] = (float *)gpu_probe_exchange_buffer(xs[d]);
     }
-    printf("RESULT kind=allreduce_peak gpus=%d gpu=all bytes=%" PRIu64 " ms=na ms_med=na gbs=%.2f frac_nominal=%.4f "
-           "frac_measured=na lanes=na match=na\n", G, best_bytes, best_bus, best_bus / NOMINAL_NVLINK_GBS);
-    for (int d = 0; d < G; ++d) NC(nc, nc->CommDestroy(comms[d]));
+    PR(gpu_probe_exchange_connect_local(xs, G));
+    if (nc->so) NC(nc, nc->CommInitAll(comms, G, devs));
+
+    for (int use_nccl = nc->so ? 1 : 0; use_nccl >= 0; --use_nccl) {
+      int ok = 0;
+      if ((rc = check_allreduce(use_nccl, nc, comms, gs, xs, bufs, G, max_bytes, &ok))) return rc;
+      for (int d = 0; d < G; ++d) { /* zeros: sums stay finite however often the prefix is reduced */
+        CU(cudaSetDevice(gs[d].dev));
+        CU(cudaMemsetAsync(bufs[d], 0, max_bytes, gs[d].st));
+      }
+      double best_bus = 0;
+      uint64_t best_bytes = 0;
+      for (uint64_t S = 1024; S <= max_bytes; S <<= 1) {
+        const int iters = S >= (1u << 20) ? o->iters : 2 * o->iters;
+        double ms = 0;
+        if ((rc = time_allreduce(use_nccl, nc, comms, gs, xs, bufs, G, S, iters, &ms))) return rc;
+        const double algbw = (double)S / (ms * 1e-3) / 1e9;
+        const double busbw = algbw * 2.0 * (G - 1) / G;
+        if (busbw > best_bus) { best_bus = busbw; best_bytes = S; }
+        printf("RESULT kind=allreduce gpus=%d gpu=all bytes=%" PRIu64 " ms=%.5f ms_med=%.5f gbs=%.2f "
+               "frac_nominal=%.4f frac_measured=na lanes=na match=na us=%.2f algbw=%.2f busbw=%.2f impl=%s\n",
+               G, S, ms, ms, busbw, busbw / NOMINAL_NVLINK_GBS, ms * 1e3, algbw, busbw,
+               use_nccl ? "nccl" : "p2p_kernel");
+      }
+      printf("RESULT kind=allreduce_peak gpus=%d gpu=all bytes=%" PRIu64 " ms=na ms_med=na gbs=%.2f frac_nominal=%.4f "
+             "frac_measured=na lanes=na match=na impl=%s\n", G, best_bytes, best_bus, best_bus / NOMINAL_NVLINK_GBS,
+             use_nccl ? "nccl" : "p2p_kernel");
+    }
+    if (nc->so)
+      for (int d = 0; d < G; ++d) NC(nc, nc->CommDestroy(comms[d]));
+    for (int d = 0; d < G; ++d) PR(gpu_probe_exchange_destroy(xs[d]));
   }
   return 0;
 }
@@ -681,7 +726,7 @@ static int run(const options *o) {
       gpu_probe_exchange *xs[MAX_GPUS];
       for (int d = 0; d < ng; ++d) {
         CU(cudaSetDevice(gs[d].dev));
-        PR(gpu_probe_exchange_create(&gs[d].xchg, d, ng));
+        PR(gpu_probe_exchange_create(&gs[d].xchg, d, ng, 0));
         xs[d] = gs[d].xchg;
       }
       PR(gpu_probe_exchange_connect_local(xs, ng));
@@ -696,7 +741,7 @@ static int run(const options *o) {
       if (have_nccl)
         for (int d = 0; d < ng; ++d) NC(&nc, nc.CommDestroy(comms[d]));
     }
-    if (o->do_sweep && have_nccl && (rc = phase_sweep(o, gs, ng, &nc))) return rc;
+    if (o->do_sweep && (rc = phase_sweep(o, gs, ng, &nc))) return rc;
     if (o->do_p2p && (rc = phase_p2p(o, gs, ng))) return rc;
   }
   return 0;

@@ -1,0 +1,155 @@
+"""K4, the probe's own fp32 allreduce over peer memory (gpu_probe_allreduce_f32), through
+the C ABI.  The result is defined exactly: every element is the fp32 sum of the ranks'
+values taken in rank order 0..G-1, and all ranks hold identical bits -- so the comparison
+with the numpy restatement below is bit-exact, no tolerance.
+
+On a 1-GPU box the ranks share cuda:0 (each on its own stream, few CTAs each so that all of
+them are resident together); with more GPUs the same tests cross NVLink."""
+import numpy as np
+import pytest
+import torch
+
+import gpuprobe
+
+pytestmark = pytest.mark.gpu
+
+
+def _devices(world):
+    g = torch.cuda.device_count()
+    return [r % g for r in range(world)] if g < world else list(range(world))
+
+
+class Group:
+    def __init__(self, world, buffer_bytes):
+        self.world, self.dev = world, _devices(world)
+        self.shared = len(set(self.dev)) < world
+        self.x, self.st = [], []
+        for r in range(world):
+            with torch.cuda.device(self.dev[r]):
+                self.x.append(gpuprobe.Exchange(r, world, buffer_bytes))
+                self.st.append(torch.cuda.Stream())
+        gpuprobe.Exchange.connect_local(self.x)
+
+    @property
+    def ctas(self):
+        return 8 if self.shared else 0  # shared device: every rank's CTAs must fit on the one GPU together
+
+    def put(self, r, arr, offset=0):
+        with torch.cuda.device(self.dev[r]):
+            t = torch.from_numpy(arr).cuda()
+            gpuprobe.p2p_copy(self.x[r].buffer + offset, t.data_ptr(), arr.nbytes, 0)
+            torch.cuda.synchronize()
+
+    def get(self, r, count, offset=0):
+        with torch.cuda.device(self.dev[r]):
+            t = torch.empty(count, dtype=torch.float32, device="cuda")
+            gpuprobe.p2p_copy(t.data_ptr(), self.x[r].buffer + offset, 4 * count, 0)
+            torch.cuda.synchronize()
+            return t.cpu().numpy()
+
+    def allreduce(self, count, offset=0, ctas=None):
+        for r in range(self.world):
+            with torch.cuda.device(self.dev[r]):
+                self.x[r].allreduce_f32(offset, count, self.ctas if ctas is None else ctas, self.st[r].cuda_stream)
+
+    def sync(self):
+        for d in set(self.dev):
+            torch.cuda.synchronize(d)
+
+    def close(self):
+        self.sync()
+        for x in self.x:
+            x.close()
+
+
+def rank_order_sum(parts):
+    s = parts[0].copy()
+    for p in parts[1:]:
+        s = (s + p).astype(np.float32)
+    return s
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 4, 8])
+@pytest.mark.parametrize("count", [1, 3, 4, 5, 1023, 4096, 65537, (1 << 20) + 2])
+def test_allreduce_is_the_rank_order_fp32_sum_on_every_rank(world, count):
+    rng = np.random.default_rng(100 * world + count % 89)
+    parts = [rng.standard_normal(count).astype(np.float32) * np.float32(10.0 ** rng.integers(-3, 4)) for _ in range(world)]
+    want = rank_order_sum(parts)
+    G = Group(world, 4 * count + 64)
+    try:
+        for r in range(world):
+            G.put(r, parts[r])
+        G.allreduce(count)
+        G.sync()
+        for r in range(world):
+            got = G.get(r, count)
+            assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (world, count, r)
+            assert G.x[r].status() == 0
+    finally:
+        G.close()
+
+
+def test_allreduce_at_an_offset_leaves_the_rest_untouched_and_repeats():
+    world, count, off = 4, 50000, 4096
+    rng = np.random.default_rng(7)
+    G = Group(world, off + 4 * count + 4096)
+    try:
+        total = (off + 4 * count + 4096) // 4
+        base = [rng.standard_normal(total).astype(np.float32) for _ in range(world)]
+        for r in range(world):
+            G.put(r, base[r])
+        cur = [b[off // 4: off // 4 + count].copy() for b in base]
+        for rep in range(5):  # back-to-back collectives on the same data: values grow, epochs advance
+            G.allreduce(count, off)
+            s = rank_order_sum(cur)
+            cur = [s.copy() for _ in range(world)]
+        G.sync()
+        for r in range(world):
+            got = G.get(r, total)
+            assert np.array_equal(got[: off // 4].view(np.uint32), base[r][: off // 4].view(np.uint32))
+            assert np.array_equal(got[off // 4 + count:].view(np.uint32), base[r][off // 4 + count:].view(np.uint32))
+            assert np.array_equal(got[off // 4: off // 4 + count].view(np.uint32), cur[r].view(np.uint32)), r
+    finally:
+        G.close()
+
+
+def test_allreduce_grid_choices_agree():
+    world, count = 2, (1 << 18) + 7
+    rng = np.random.default_rng(11)
+    parts = [rng.standard_normal(count).astype(np.float32) for _ in range(world)]
+    want = rank_order_sum(parts)
+    G = Group(world, 4 * count)
+    try:
+        for ctas in (1, 2, 7, 16):
+            for r in range(world):
+                G.put(r, parts[r])
+            G.allreduce(count, 0, ctas)
+            G.sync()
+            for r in range(world):
+                assert np.array_equal(G.get(r, count).view(np.uint32), want.view(np.uint32)), (ctas, r)
+    finally:
+        G.close()
+
+
+def test_allreduce_argument_errors_and_missing_peer():
+    G = Group(2, 1 << 16)
+    try:
+        x = G.x[0]
+        with torch.cuda.device(G.dev[0]):
+            for args, rc in (((8, 4), gpuprobe.EINVAL),               # offset not 16-byte aligned
+                             ((0, (1 << 14) + 1), gpuprobe.ETOOBIG),  # beyond the buffer
+                             ((1 << 17, 1), gpuprobe.ETOOBIG)):
+                with pytest.raises(gpuprobe.ProbeError) as ei:
+                    x.allreduce_f32(*args)
+                assert ei.value.rc == rc
+            nobuf = gpuprobe.Exchange(0, 1)
+            with pytest.raises(gpuprobe.ProbeError) as ei:
+                nobuf.allreduce_f32(0, 4)
+            assert ei.value.rc == gpuprobe.EINVAL
+            nobuf.close()
+            x.set_timeout_ms(50)
+            x.allreduce_f32(0, 1024, 4, G.st[0].cuda_stream)  # rank 1 never calls
+        G.sync()
+        assert x.status() == gpuprobe.ETIMEDOUT
+    finally:
+        G.close()

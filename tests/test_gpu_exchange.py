@@ -164,9 +164,9 @@ def test_exchange_argument_and_state_errors():
     L = gpuprobe.lib()
     import ctypes
     h = ctypes.c_void_p()
-    assert L.gpu_probe_exchange_create(ctypes.byref(h), 0, 0) == gpuprobe.EINVAL
-    assert L.gpu_probe_exchange_create(ctypes.byref(h), 2, 2) == gpuprobe.EINVAL
-    assert L.gpu_probe_exchange_create(ctypes.byref(h), 0, gpuprobe.EXCHANGE_MAX_RANKS + 1) == gpuprobe.EINVAL
+    assert L.gpu_probe_exchange_create(ctypes.byref(h), 0, 0, 0) == gpuprobe.EINVAL
+    assert L.gpu_probe_exchange_create(ctypes.byref(h), 2, 2, 0) == gpuprobe.EINVAL
+    assert L.gpu_probe_exchange_create(ctypes.byref(h), 0, gpuprobe.EXCHANGE_MAX_RANKS + 1, 0) == gpuprobe.EINVAL
     x = gpuprobe.Exchange(0, 2)  # created but never connected
     try:
         t, ws, out = from_np(np.arange(8, dtype=np.uint64)), workspace(), lanes_buf()

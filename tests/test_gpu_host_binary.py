@@ -76,8 +76,10 @@ def test_multi_gpu_probe_sharded_checksum_sweep_and_p2p():
     for x in combos.values():
         assert x["lanes"] == hexw and x["match"] == "1"
     assert all(x["match"] == "1" for x in by["allreduce_check"])
-    sizes = [int(x["bytes"]) for x in by["allreduce"] if x["gpus"] == "2"]
-    assert sizes == [1 << k for k in range(10, 27)]
+    assert {x["impl"] for x in by["allreduce_check"]} == {"nccl", "p2p_kernel"}
+    for impl in ("nccl", "p2p_kernel"):
+        sizes = [int(x["bytes"]) for x in by["allreduce"] if x["gpus"] == "2" and x["impl"] == impl]
+        assert sizes == [1 << k for k in range(10, 27)], impl
     assert all(x["match"] == "1" for x in by["p2p"])
     assert {x["mode"] for x in by["p2p"]} == {"sm_kernel", "copy_engine"}
 

@@ -134,10 +134,10 @@ int gpu_probe_p2p_copy(void *dst, const void *src, uint64_t bytes, void *stream)
  * own mailbox and writes the global sum to out_lanes -- every rank ends with the same
  * two words, bit-identical to a single-GPU checksum of the whole buffer.
  *
- * A gpu_probe_exchange is one rank's symmetric segment -- a 256 KiB header (lanes mailbox,
- * barrier flags) plus an optional data buffer of `buffer_bytes` (the allreduce operand) --
- * and the addresses of the peers' segments.
- *   create          [blocking, ALLOCATES 256 KiB + buffer_bytes] on the current device.
+ * A gpu_probe_exchange is one rank's symmetric segment -- a 512 KiB header (lanes mailbox,
+ * barrier flags) plus, when buffer_bytes > 0, a data buffer (the allreduce operand) and
+ * 2 x world x min(buffer_bytes, 2 MiB) of staging -- and the addresses of the peers' segments.
+ *   create          [blocking, ALLOCATES the segment] on the current device.
  *   connect_local   ranks living in one process: enables peer access both ways and
  *                   hands raw pointers around.  xs[r] must be rank r.
  *   export / connect_ipc   one process per GPU: export gives this rank's CUDA IPC
@@ -168,14 +168,22 @@ void *gpu_probe_exchange_buffer(gpu_probe_exchange *x);
 uint64_t gpu_probe_exchange_buffer_bytes(gpu_probe_exchange *x);
 
 /* K4  in-place fp32 sum allreduce of `count` elements at buffer + offset_bytes (16-byte
- * aligned offset) over all ranks, in ONE kernel over NVLink peer memory: rank r pulls its
- * slice from every rank, adds in rank order 0..G-1 and pushes the sums back to every rank.
- * All ranks end with bit-identical data.  `ctas` = 0 lets the library size the grid (every
- * rank must pass the same count and ctas).  World sizes 1..8.  This is the probe's own
- * collective, timed beside NCCL's allreduce (SURVEY 8d "Allreduce sweep"); same rules as the
- * *_exchange calls above. */
+ * aligned offset) over all ranks, in ONE kernel over NVLink peer memory.  All ranks end with
+ * bit-identical data: every element is the fp32 sum of the ranks' values in rank order.
+ *   PULL_PUSH  rank r pulls its slice from every rank, adds, pushes the sums back to every
+ *              rank; 2(G-1)/G x bytes per direction per GPU -- the bandwidth algorithm.
+ *   PUSH       every rank pushes its whole operand into staging on every peer and adds up
+ *              what lands in its own; one NVLink traversal -- the latency algorithm.
+ *              Needs count % 4 == 0 and 4*count <= 2 MiB, else GPU_PROBE_ETOOBIG.
+ *   AUTO       PUSH below a per-world-size threshold, PULL_PUSH above.
+ * `ctas` = 0 lets the library size the grid.  Every rank must pass the same count, algo and
+ * ctas.  World sizes 1..8.  This is the probe's own collective, timed beside NCCL's
+ * allreduce (SURVEY 8d "Allreduce sweep"); same rules as the *_exchange calls above. */
+#define GPU_PROBE_ALLREDUCE_AUTO 0
+#define GPU_PROBE_ALLREDUCE_PULL_PUSH 1
+#define GPU_PROBE_ALLREDUCE_PUSH 2
 int gpu_probe_allreduce_f32(gpu_probe_exchange *x, uint64_t offset_bytes, uint64_t count,
-                            int ctas, void *stream);
+                            int algo, int ctas, void *stream);
 
 /* K2 + lanes exchange in one launch.  Arguments as gpu_probe_checksum_u64; out_lanes
  * receives the sum over ALL ranks.  Must be called with x's device current. */

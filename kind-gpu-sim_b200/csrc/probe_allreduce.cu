@@ -35,8 +35,9 @@ struct AllreduceArgs {
   unsigned char *seg[kMaxRanks];  // segment base of rank p as THIS GPU addresses it
   int rank, world;
   unsigned long long timeout_ns;
-  uint64_t offset_bytes;  // operand = payload + offset_bytes
+  uint64_t operand_off;   // operand = segment + operand_off (payload offset + caller's offset)
   uint64_t count;         // fp32 elements
+  uint64_t stage_bytes;   // one staging slot (one-shot algorithm); staging = segment + kHeaderBytes
 };
 
 __device__ __forceinline__ float4 ld_peer(const float4 *p) {  // system-coherent, never from a stale L1 line
@@ -61,16 +62,17 @@ __device__ __forceinline__ void st_peer(float *p, float v) {
 // CTA b of this rank meets CTA b of every peer.  Returns false on timeout.
 // Release/acquire at system scope on the flag; the __syncthreads on either side extend
 // that ordering to every thread of the CTA (cumulativity).
+template <size_t FLAGS_OFFSET_WORDS = kFlagsOffsetWords>
 __device__ __forceinline__ bool cta_barrier(const AllreduceArgs &a, uint64_t epoch) {
   __shared__ int timed_out;
   if (threadIdx.x == 0) timed_out = 0;
   __syncthreads();
   if (threadIdx.x < a.world) {
     const int p = threadIdx.x;
-    uint64_t *theirs = reinterpret_cast<uint64_t *>(a.seg[p]) + kFlagsOffsetWords + size_t(blockIdx.x) * kMaxRanks + a.rank;
+    uint64_t *theirs = reinterpret_cast<uint64_t *>(a.seg[p]) + FLAGS_OFFSET_WORDS + size_t(blockIdx.x) * kMaxRanks + a.rank;
     __threadfence_system();
     st_release_sys(theirs, epoch);
-    const uint64_t *mine = reinterpret_cast<const uint64_t *>(a.seg[a.rank]) + kFlagsOffsetWords +
+    const uint64_t *mine = reinterpret_cast<const uint64_t *>(a.seg[a.rank]) + FLAGS_OFFSET_WORDS +
                            size_t(blockIdx.x) * kMaxRanks + p;
     const unsigned long long t0 = global_ns();
     while (ld_acquire_sys(mine) < epoch) {
@@ -86,7 +88,7 @@ __device__ __forceinline__ void reduce_broadcast(const AllreduceArgs &a, uint64_
   // vectors [v_lo, v_hi) of the operand belong to this rank; CTAs stride over them
   float4 *buf[G];
 #pragma unroll
-  for (int p = 0; p < G; ++p) buf[p] = reinterpret_cast<float4 *>(a.seg[p] + kPayloadOffsetBytes + a.offset_bytes);
+  for (int p = 0; p < G; ++p) buf[p] = reinterpret_cast<float4 *>(a.seg[p] + a.operand_off);
   const uint64_t tile = uint64_t(kArThreads) * U;
   for (uint64_t base = v_lo + blockIdx.x * tile; base < v_hi; base += uint64_t(gridDim.x) * tile) {
     float4 v[U][G];
@@ -133,11 +135,11 @@ allreduce_f32_kernel(const AllreduceArgs a) {
       float s = 0.f;
 #pragma unroll
       for (int p = 0; p < G; ++p) {
-        const float x = ld_peer(reinterpret_cast<const float *>(a.seg[p] + kPayloadOffsetBytes + a.offset_bytes) + i);
+        const float x = ld_peer(reinterpret_cast<const float *>(a.seg[p] + a.operand_off) + i);
         s = p == 0 ? x : s + x;
       }
 #pragma unroll
-      for (int p = 0; p < G; ++p) st_peer(reinterpret_cast<float *>(a.seg[p] + kPayloadOffsetBytes + a.offset_bytes) + i, s);
+      for (int p = 0; p < G; ++p) st_peer(reinterpret_cast<float *>(a.seg[p] + a.operand_off) + i, s);
     }
     ok = cta_barrier(a, e + 2);  // every push has landed everywhere before any rank's kernel ends
   }
@@ -147,10 +149,72 @@ allreduce_f32_kernel(const AllreduceArgs a) {
   }
 }
 
+// ---- one-shot variant for small operands ---------------------------------------------
+// Latency, not bandwidth, decides below a few MiB, and the pull/push kernel above costs
+// four NVLink traversals (barrier, pull round trip, push, barrier).  Here every rank PUSHES
+// its whole operand into slot `rank` of a staging area on every peer, raises one flag per
+// CTA, and then adds up the G slots that landed in its own staging area -- one traversal
+// plus the fence.  Every rank computes every element itself, in rank order, so the ranks
+// still agree bit for bit.  Staging is double-buffered by call parity (same argument as the
+// lanes mailbox), so no trailing barrier is needed; peers never read the operand itself.
+template <int G, int U>
+__global__ void __launch_bounds__(kArThreads)
+allreduce_f32_push_kernel(const AllreduceArgs a) {
+  uint64_t *hdr = reinterpret_cast<uint64_t *>(a.seg[a.rank]);
+  __shared__ uint64_t epoch0;
+  if (threadIdx.x == 0) epoch0 = hdr[kPushEpochOffsetWords + blockIdx.x];
+  __syncthreads();
+  const uint64_t e = epoch0 + 1;
+  const size_t slot_set = kHeaderBytes + size_t(e & 1) * G * a.stage_bytes;  // staging[e & 1]
+  float4 *mine_op = reinterpret_cast<float4 *>(a.seg[a.rank] + a.operand_off);
+  const uint64_t nvec = (a.count + 3) / 4;  // the operand is padded to 16 bytes inside the buffer (see entry point)
+  float4 own[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const uint64_t i = (uint64_t(u) * gridDim.x + blockIdx.x) * kArThreads + threadIdx.x;
+    if (i < nvec) {
+      own[u] = mine_op[i];
+#pragma unroll
+      for (int q = 1; q < G; ++q) {  // start with the next rank: spread the first stores over the links
+        const int p = (a.rank + q) % G;
+        st_peer(reinterpret_cast<float4 *>(a.seg[p] + slot_set + size_t(a.rank) * a.stage_bytes) + i, own[u]);
+      }
+    }
+  }
+  const bool ok = cta_barrier<kPushFlagsOffsetWords>(a, e);  // my stores have landed; the peers' too
+  if (ok) {
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint64_t i = (uint64_t(u) * gridDim.x + blockIdx.x) * kArThreads + threadIdx.x;
+      if (i < nvec) {
+        float4 s;
+#pragma unroll
+        for (int p = 0; p < G; ++p) {
+          const float4 x = p == a.rank ? own[u]
+                                       : ld_peer(reinterpret_cast<const float4 *>(a.seg[a.rank] + slot_set + size_t(p) * a.stage_bytes) + i);
+          if (p == 0) s = x;
+          else { s.x += x.x; s.y += x.y; s.z += x.z; s.w += x.w; }
+        }
+        mine_op[i] = s;
+      }
+    }
+  }
+  if (threadIdx.x == 0) {
+    hdr[kPushEpochOffsetWords + blockIdx.x] = e;
+    if (!ok) hdr[1] = 1;
+  }
+}
+
+constexpr int kPushU = 2;  // vectors per thread in the one-shot kernel: grid * 512 * kPushU * 16 B covers the operand
+
 template <int G>
-static int launch_allreduce(const AllreduceArgs &a, unsigned grid, cudaStream_t st) {
-  constexpr int U = G <= 2 ? 8 : (G <= 4 ? 4 : 2);  // G*U 16-byte loads in flight per thread
-  allreduce_f32_kernel<G, U><<<grid, kArThreads, 0, st>>>(a);
+static int launch_allreduce(const AllreduceArgs &a, int algo, unsigned grid, cudaStream_t st) {
+  if (algo == GPU_PROBE_ALLREDUCE_PUSH) {
+    allreduce_f32_push_kernel<G, kPushU><<<grid, kArThreads, 0, st>>>(a);
+  } else {
+    constexpr int U = G <= 2 ? 8 : (G <= 4 ? 4 : 2);  // G*U 16-byte loads in flight per thread
+    allreduce_f32_kernel<G, U><<<grid, kArThreads, 0, st>>>(a);
+  }
   return int(cudaGetLastError());
 }
 
@@ -158,42 +222,81 @@ static int launch_allreduce(const AllreduceArgs &a, unsigned grid, cudaStream_t 
 
 using namespace probe;
 
-extern "C" int gpu_probe_allreduce_f32(gpu_probe_exchange *x, uint64_t offset_bytes, uint64_t count, int ctas,
-                                       void *stream) {
+static int device_sms(int dev, int *sms) {
+  static int cache[64];
+  if (dev >= 0 && dev < 64 && cache[dev] > 0) { *sms = cache[dev]; return 0; }
+  int v = 0;
+  cudaError_t e = cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+  if (e != cudaSuccess) return int(e);
+  if (dev >= 0 && dev < 64) cache[dev] = v;
+  *sms = v;
+  return 0;
+}
+
+// Operand size (bytes) up to which AUTO takes the one-shot kernel.  It moves (G-1) x the
+// operand per GPU instead of 2(G-1)/G x, so the crossover falls as G grows
+// (profiles/allreduce_sweep_r1.md).
+static uint64_t push_threshold_bytes(int world) {
+  return world <= 2 ? (2u << 20) : world <= 4 ? (1u << 20) : (512u << 10);
+}
+
+extern "C" int gpu_probe_allreduce_f32(gpu_probe_exchange *x, uint64_t offset_bytes, uint64_t count, int algo,
+                                       int ctas, void *stream) {
   if (!live(x) || !x->connected) return GPU_PROBE_ENOTREADY;
   if (x->buffer_bytes == 0 || (offset_bytes & 15)) return GPU_PROBE_EINVAL;
   if (offset_bytes > x->buffer_bytes || count > (x->buffer_bytes - offset_bytes) / 4) return GPU_PROBE_ETOOBIG;
   if (ctas < 0 || ctas > kMaxCommCtas) return GPU_PROBE_EINVAL;
+  if (algo < GPU_PROBE_ALLREDUCE_AUTO || algo > GPU_PROBE_ALLREDUCE_PUSH) return GPU_PROBE_EINVAL;
   int dev = -1;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return int(e);
   if (dev != x->device) return GPU_PROBE_EINVAL;
   if (count == 0) return 0;  // every rank passes the same count, so every rank skips
+  int sms = 0;
+  int rc = device_sms(dev, &sms);
+  if (rc) return rc;
   AllreduceArgs a;
   std::memset(&a, 0, sizeof(a));
   for (int p = 0; p < x->world; ++p) a.seg[p] = reinterpret_cast<unsigned char *>(x->peer[p]);
   a.rank = x->rank; a.world = x->world; a.timeout_ns = x->timeout_ns;
-  a.offset_bytes = offset_bytes; a.count = count;
-  // Grid: a function of (count, world, SM count) only, so every rank picks the same one --
-  // CTA b must exist on every rank.  All CTAs are co-resident (<= 1 per SM).
-  int sms = 0;
-  e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  if (e != cudaSuccess) return int(e);
-  const uint64_t slice_vecs = (count / 4 + x->world - 1) / x->world;
-  uint64_t want = (slice_vecs + kArThreads - 1) / kArThreads;  // at least one vector per thread
-  if (want < 1) want = 1;
-  unsigned grid = ctas > 0 ? unsigned(ctas) : unsigned(want < uint64_t(sms) ? want : uint64_t(sms));
-  if (grid > unsigned(sms)) grid = unsigned(sms);
+  a.operand_off = x->payload_offset + offset_bytes; a.count = count; a.stage_bytes = x->stage_bytes;
+  const uint64_t bytes = 4 * count;
+  // The one-shot kernel works on whole 16-byte vectors; the buffer is padded to 256 bytes, so
+  // the up-to-3 floats past `count` exist -- but they belong to the caller, so only take the
+  // one-shot path when the operand is a whole number of vectors.
+  const bool push_ok = (count % 4 == 0) && bytes <= x->stage_bytes;
+  if (algo == GPU_PROBE_ALLREDUCE_PUSH && !push_ok) return GPU_PROBE_ETOOBIG;
+  if (algo == GPU_PROBE_ALLREDUCE_AUTO)
+    algo = (push_ok && bytes <= push_threshold_bytes(x->world)) ? GPU_PROBE_ALLREDUCE_PUSH : GPU_PROBE_ALLREDUCE_PULL_PUSH;
+  // Grid: a function of (count, world, algo, ctas, SM count) only, so every rank picks the
+  // same one -- CTA b must exist on every rank.  All CTAs are co-resident (<= 1 per SM).
+  unsigned grid;
+  if (algo == GPU_PROBE_ALLREDUCE_PUSH) {
+    const uint64_t nvec = count / 4;
+    const uint64_t need = (nvec + uint64_t(kArThreads) * kPushU - 1) / (uint64_t(kArThreads) * kPushU);  // must cover the operand
+    if (need > uint64_t(kMaxCommCtas)) return GPU_PROBE_ETOOBIG;
+    uint64_t g = (nvec + kArThreads - 1) / kArThreads;   // one vector per thread while the SMs last
+    if (g > uint64_t(sms)) g = uint64_t(sms);
+    if (ctas > 0) g = uint64_t(ctas);
+    if (g < need) g = need;
+    grid = unsigned(g);
+  } else {
+    const uint64_t slice_vecs = (count / 4 + x->world - 1) / x->world;
+    uint64_t want = (slice_vecs + kArThreads - 1) / kArThreads;  // at least one vector per thread
+    if (want < 1) want = 1;
+    grid = ctas > 0 ? unsigned(ctas) : unsigned(want < uint64_t(sms) ? want : uint64_t(sms));
+    if (grid > unsigned(sms)) grid = unsigned(sms);
+  }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (x->world) {
-    case 1: return launch_allreduce<1>(a, grid, st);
-    case 2: return launch_allreduce<2>(a, grid, st);
-    case 3: return launch_allreduce<3>(a, grid, st);
-    case 4: return launch_allreduce<4>(a, grid, st);
-    case 5: return launch_allreduce<5>(a, grid, st);
-    case 6: return launch_allreduce<6>(a, grid, st);
-    case 7: return launch_allreduce<7>(a, grid, st);
-    case 8: return launch_allreduce<8>(a, grid, st);
+    case 1: return launch_allreduce<1>(a, algo, grid, st);
+    case 2: return launch_allreduce<2>(a, algo, grid, st);
+    case 3: return launch_allreduce<3>(a, algo, grid, st);
+    case 4: return launch_allreduce<4>(a, algo, grid, st);
+    case 5: return launch_allreduce<5>(a, algo, grid, st);
+    case 6: return launch_allreduce<6>(a, algo, grid, st);
+    case 7: return launch_allreduce<7>(a, algo, grid, st);
+    case 8: return launch_allreduce<8>(a, algo, grid, st);
     default: return GPU_PROBE_EINVAL;  // more than 8 ranks: not one NVSwitch domain of this probe
   }
 }

@@ -126,21 +126,27 @@ constexpr size_t kWorkspaceBytes =
 //                    is chosen by epoch parity.  Two buffers suffice: a rank can only start
 //                    call k+2 after every peer has written call k+1, which each peer does
 //                    after it finished reading call k.
-//   8 KiB  cta_epoch[kMaxCommCtas]            barrier epoch of CTA b on this GPU (local only)
-//   16 KiB flags[kMaxCommCtas][kMaxRanks]     flags[b][p] = last barrier epoch CTA b of rank p
+//   8 KiB   cta_epoch[kMaxCommCtas]           barrier epoch of CTA b on this GPU (local only)
+//   16 KiB  push_epoch[kMaxCommCtas]          call count of CTA b in the one-shot allreduce (local)
+//   32 KiB  flags[kMaxCommCtas][kMaxRanks]    flags[b][p] = last barrier epoch CTA b of rank p
 //                                             signalled to this GPU (written by p, polled here)
-//   256 KiB payload                           the symmetric data buffer (allreduce operand)
+//   160 KiB push_flags[kMaxCommCtas][kMaxRanks]  same, for the one-shot allreduce
+//   512 KiB staging[2][world][stage_bytes]    one-shot allreduce: rank p's operand lands in slot p
+//   512 KiB + 2*world*stage_bytes: payload    the symmetric data buffer (allreduce operand)
 constexpr int kMaxRanks = 16;
 constexpr int kSlotWords = 4;
 constexpr int kMailboxSlotsOffsetWords = 32;
 constexpr size_t kMailboxBytes = sizeof(uint64_t) * (kMailboxSlotsOffsetWords + 2 * kMaxRanks * kSlotWords);
 constexpr int kMaxCommCtas = 1024;
 constexpr size_t kCtaEpochOffsetWords = 8192 / 8;
-constexpr size_t kFlagsOffsetWords = 16384 / 8;
-constexpr size_t kPayloadOffsetBytes = 256 * 1024;
+constexpr size_t kPushEpochOffsetWords = 16384 / 8;
+constexpr size_t kFlagsOffsetWords = 32768 / 8;
+constexpr size_t kPushFlagsOffsetWords = 163840 / 8;
+constexpr size_t kHeaderBytes = 512 * 1024;
+constexpr size_t kMaxStageBytes = 2u << 20;  // largest operand the one-shot allreduce takes
 static_assert(kMailboxBytes <= 8192, "mailbox overlaps the epoch table");
-static_assert(kCtaEpochOffsetWords + kMaxCommCtas <= kFlagsOffsetWords, "epoch table overlaps the flags");
-static_assert((kFlagsOffsetWords + size_t(kMaxCommCtas) * kMaxRanks) * 8 <= kPayloadOffsetBytes, "flags overlap the payload");
+static_assert(kFlagsOffsetWords + size_t(kMaxCommCtas) * kMaxRanks <= kPushFlagsOffsetWords, "flags overlap");
+static_assert((kPushFlagsOffsetWords + size_t(kMaxCommCtas) * kMaxRanks) * 8 <= kHeaderBytes, "flags overlap the staging");
 
 struct ExchangeArgs {           // passed to kernels by value; world == 0: no exchange
   uint64_t *mailbox[kMaxRanks]; // mailbox[p]: rank p's segment base as THIS GPU addresses it

@@ -46,9 +46,11 @@ extern "C" int gpu_probe_exchange_create(gpu_probe_exchange **out, int rank, int
   x->device = dev; x->rank = rank; x->world = world;
   x->timeout_ns = 10ull * 1000 * 1000 * 1000;  // a peer that is 10 s late is not coming
   x->buffer_bytes = buffer_bytes;
-  // header (mailbox, barrier epochs and flags) and payload are ONE allocation: one IPC handle maps both
-  e = cudaMalloc(reinterpret_cast<void **>(&x->mailbox), kPayloadOffsetBytes + buffer_bytes);
-  if (e == cudaSuccess) e = cudaMemset(x->mailbox, 0, kPayloadOffsetBytes);
+  x->stage_bytes = buffer_bytes < kMaxStageBytes ? buffer_bytes : kMaxStageBytes;
+  x->payload_offset = kHeaderBytes + 2 * uint64_t(world) * x->stage_bytes;
+  // header (mailbox, barrier epochs and flags), staging and payload are ONE allocation: one IPC handle maps all
+  e = cudaMalloc(reinterpret_cast<void **>(&x->mailbox), x->payload_offset + buffer_bytes);
+  if (e == cudaSuccess) e = cudaMemset(x->mailbox, 0, kHeaderBytes);
   if (e == cudaSuccess) e = cudaDeviceSynchronize();  // zeroed before any peer can learn the address
   if (e != cudaSuccess) {
     if (x->mailbox) cudaFree(x->mailbox);
@@ -148,7 +150,7 @@ extern "C" int gpu_probe_exchange_destroy(gpu_probe_exchange *x) {
 
 extern "C" void *gpu_probe_exchange_buffer(gpu_probe_exchange *x) {
   if (!live(x) || x->buffer_bytes == 0) return nullptr;
-  return reinterpret_cast<unsigned char *>(x->mailbox) + kPayloadOffsetBytes;
+  return reinterpret_cast<unsigned char *>(x->mailbox) + x->payload_offset;
 }
 
 extern "C" uint64_t gpu_probe_exchange_buffer_bytes(gpu_probe_exchange *x) { return live(x) ? x->buffer_bytes : 0; }

@@ -15,6 +15,8 @@ struct gpu_probe_exchange {
   bool connected;
   uint64_t *mailbox;            // this rank's segment (cudaMalloc on `device`): header + payload
   uint64_t buffer_bytes;        // payload size (0: lanes exchange only)
+  uint64_t stage_bytes;         // one staging slot of the one-shot allreduce (0 when there is no payload)
+  uint64_t payload_offset;      // payload = segment + payload_offset (same on every rank)
   uint64_t *peer[kMaxRanks];    // every rank's mailbox as addressed from `device`
   bool ipc_opened[kMaxRanks];   // peer[p] came from cudaIpcOpenMemHandle
   unsigned long long timeout_ns;

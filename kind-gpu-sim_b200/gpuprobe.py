@@ -24,6 +24,7 @@ VARIANTS = {"auto": VARIANT_AUTO, "ldg128": VARIANT_LDG, "tma": VARIANT_TMA, "ld
 
 EINVAL, EALIGN, ETOOBIG, ENOTREADY, ETIMEDOUT = -100, -101, -102, -103, -104
 EXCHANGE_MAX_RANKS, EXCHANGE_HANDLE_BYTES = 16, 64
+ALLREDUCE_AUTO, ALLREDUCE_PULL_PUSH, ALLREDUCE_PUSH = 0, 1, 2
 
 _u64 = ctypes.c_uint64
 _vp = ctypes.c_void_p
@@ -68,7 +69,7 @@ def lib() -> ctypes.CDLL:
         L.gpu_probe_exchange_buffer.restype = _vp
         L.gpu_probe_exchange_buffer_bytes.argtypes = [_vp]
         L.gpu_probe_exchange_buffer_bytes.restype = _u64
-        L.gpu_probe_allreduce_f32.argtypes = [_vp, _u64, _u64, ctypes.c_int, _vp]
+        L.gpu_probe_allreduce_f32.argtypes = [_vp, _u64, _u64, ctypes.c_int, ctypes.c_int, _vp]
         L.gpu_probe_allreduce_f32.restype = ctypes.c_int
         L.gpu_probe_exchange_connect_local.argtypes = [ctypes.POINTER(_vp), ctypes.c_int]
         L.gpu_probe_exchange_export.argtypes = [_vp, ctypes.c_char_p]
@@ -192,8 +193,11 @@ class Exchange:
     def buffer_bytes(self) -> int:
         return int(lib().gpu_probe_exchange_buffer_bytes(self._h))
 
-    def allreduce_f32(self, offset_bytes: int, count: int, ctas: int = 0, stream: int = 0) -> None:
-        _check(lib().gpu_probe_allreduce_f32(self._h, offset_bytes, count, ctas, stream), "gpu_probe_allreduce_f32")
+    def allreduce_f32(self, offset_bytes: int, count: int, ctas: int = 0, stream: int = 0,
+                      algo: int = 0) -> None:
+        """algo: ALLREDUCE_AUTO / ALLREDUCE_PULL_PUSH / ALLREDUCE_PUSH."""
+        _check(lib().gpu_probe_allreduce_f32(self._h, offset_bytes, count, algo, ctas, stream),
+               "gpu_probe_allreduce_f32")
 
     @staticmethod
     def connect_local(xs: "list[Exchange]") -> None:

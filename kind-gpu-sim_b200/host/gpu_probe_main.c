@@ -61,6 +61,8 @@ typedef struct {
   int do_sweep, do_p2p, do_sharded;
   double measured_hbm_gbs; /* 0: unknown -> frac_measured=na */
   int max_gpus;            /* use at most this many of the visible GPUs (0: all) */
+  int allreduce_algo;      /* GPU_PROBE_ALLREDUCE_* for the probe's own allreduce */
+  const char *allreduce_algo_name;
 } options;
 
 static int g_status = RC_OK; /* first failure wins */
@@ -82,7 +84,7 @@ static void die_usage(const char *fmt, ...) {
           "\nusage: gpu-probe [--expect-gpus=N] [--bytes=B] [--iters=K] [--warmup=W]\n"
           "                 [--variant=auto|ldg128|tma|ldg256] [--max-gpus=N]\n"
           "                 [--sweep-max-bytes=B] [--p2p-bytes=B] [--no-sweep] [--no-p2p] [--no-sharded]\n"
-          "                 [--measured-hbm-gbs=X]\n");
+          "                 [--measured-hbm-gbs=X] [--allreduce-algo=auto|pull_push|push]\n");
   printf("PROBE FAIL rc=%d\n", RC_USAGE);
   exit(RC_USAGE);
 }
@@ -115,6 +117,8 @@ static void parse_options(int argc, char **argv, options *o) {
   o->do_sweep = o->do_p2p = o->do_sharded = 1;
   o->measured_hbm_gbs = 0.0;
   o->max_gpus = 0;
+  o->allreduce_algo = GPU_PROBE_ALLREDUCE_AUTO;
+  o->allreduce_algo_name = "auto";
   for (int i = 1; i < argc; ++i) {
     const char *a = argv[i], *v;
     if ((v = flag_value(a, "--expect-gpus"))) o->expect_gpus = (int)parse_u64("--expect-gpus", v);
@@ -132,6 +136,12 @@ static void parse_options(int argc, char **argv, options *o) {
       else if (!strcmp(v, "tma")) o->variant = GPU_PROBE_VARIANT_TMA;
       else if (!strcmp(v, "ldg256")) o->variant = GPU_PROBE_VARIANT_LDG256;
       else die_usage("--variant: unknown variant '%s'", v);
+    } else if ((v = flag_value(a, "--allreduce-algo"))) {
+      o->allreduce_algo_name = v;
+      if (!strcmp(v, "auto")) o->allreduce_algo = GPU_PROBE_ALLREDUCE_AUTO;
+      else if (!strcmp(v, "pull_push")) o->allreduce_algo = GPU_PROBE_ALLREDUCE_PULL_PUSH;
+      else if (!strcmp(v, "push")) o->allreduce_algo = GPU_PROBE_ALLREDUCE_PUSH;
+      else die_usage("--allreduce-algo: unknown algorithm '%s'", v);
     } else if (!strcmp(a, "--no-sweep")) o->do_sweep = 0;
     else if (!strcmp(a, "--no-p2p")) o->do_p2p = 0;
     else if (!strcmp(a, "--no-sharded")) o->do_sharded = 0;
@@ -457,7 +467,7 @@ static int phase_sharded(const options *o, gpu_state *gs, int ng, uint64_t n, nc
 /* ------------- phase C: allreduce sweep at 2/4/8 GPUs -- NCCL and the probe's own K4 */
 /* One timed series: `iters` back-to-back in-place allreduces of S bytes on every GPU of the
  * group, bracketed by events on each GPU's stream; per-iteration time = slowest GPU. */
-static int time_allreduce(int use_nccl, nccl_api *nc, ncclComm_t *comms, gpu_state *gs, gpu_probe_exchange **xs,
+static int time_allreduce(const options *o, int use_nccl, nccl_api *nc, ncclComm_t *comms, gpu_state *gs, gpu_probe_exchange **xs,
                           float **bufs, int G, uint64_t S, int iters, double *ms_out) {
   int rc;
   for (int i = -5; i < iters; ++i) {
@@ -474,7 +484,7 @@ static int time_allreduce(int use_nccl, nccl_api *nc, ncclComm_t *comms, gpu_sta
     } else {
       for (int d = 0; d < G; ++d) {
         CU(cudaSetDevice(gs[d].dev));
-        PR(gpu_probe_allreduce_f32(xs[d], 0, S / 4, 0, gs[d].st));
+        PR(gpu_probe_allreduce_f32(xs[d], 0, S / 4, o->allreduce_algo, 0, gs[d].st));
       }
     }
   }
@@ -495,7 +505,7 @@ static int time_allreduce(int use_nccl, nccl_api *nc, ncclComm_t *comms, gpu_sta
 }
 
 /* Integer-valued floats in, closed-form sum out: exact in fp32 whatever the reduction order. */
-static int check_allreduce(int use_nccl, nccl_api *nc, ncclComm_t *comms, gpu_state *gs, gpu_probe_exchange **xs,
+static int check_allreduce(const options *o, int use_nccl, nccl_api *nc, ncclComm_t *comms, gpu_state *gs, gpu_probe_exchange **xs,
                            float **bufs, int G, uint64_t max_bytes, int *ok_out) {
   enum { CHECK_ELEMS = (1 << 18) + 3 };
   int rc;
@@ -516,7 +526,7 @@ static int check_allreduce(int use_nccl, nccl_api *nc, ncclComm_t *comms, gpu_st
   } else {
     for (int d = 0; d < G; ++d) {
       CU(cudaSetDevice(gs[d].dev));
-      PR(gpu_probe_allreduce_f32(xs[d], 0, celems, 0, gs[d].st));
+      PR(gpu_probe_allreduce_f32(xs[d], 0, celems, o->allreduce_algo == GPU_PROBE_ALLREDUCE_PUSH ? GPU_PROBE_ALLREDUCE_AUTO : o->allreduce_algo, 0, gs[d].st));
     }
   }
   if ((rc = sync_all(gs, G))) return rc;
@@ -559,7 +569,7 @@ static int phase_sweep(const options *o, gpu_state *gs, int ng, nccl_api *nc) {
 
     for (int use_nccl = nc->so ? 1 : 0; use_nccl >= 0; --use_nccl) {
       int ok = 0;
-      if ((rc = check_allreduce(use_nccl, nc, comms, gs, xs, bufs, G, max_bytes, &ok))) return rc;
+      if ((rc = check_allreduce(o, use_nccl, nc, comms, gs, xs, bufs, G, max_bytes, &ok))) return rc;
       for (int d = 0; d < G; ++d) { /* zeros: sums stay finite however often the prefix is reduced */
         CU(cudaSetDevice(gs[d].dev));
         CU(cudaMemsetAsync(bufs[d], 0, max_bytes, gs[d].st));
@@ -569,7 +579,8 @@ static int phase_sweep(const options *o, gpu_state *gs, int ng, nccl_api *nc) {
       for (uint64_t S = 1024; S <= max_bytes; S <<= 1) {
         const int iters = S >= (1u << 20) ? o->iters : 2 * o->iters;
         double ms = 0;
-        if ((rc = time_allreduce(use_nccl, nc, comms, gs, xs, bufs, G, S, iters, &ms))) return rc;
+        if (!use_nccl && o->allreduce_algo == GPU_PROBE_ALLREDUCE_PUSH && S > (2u << 20)) break; /* one-shot limit */
+        if ((rc = time_allreduce(o, use_nccl, nc, comms, gs, xs, bufs, G, S, iters, &ms))) return rc;
         const double algbw = (double)S / (ms * 1e-3) / 1e9;
         const double busbw = algbw * 2.0 * (G - 1) / G;
         if (busbw > best_bus) { best_bus = busbw; best_bytes = S; }

@@ -66,7 +66,7 @@ def test_argument_validation_needs_no_gpu():
     assert L.gpu_probe_exchange_create(ctypes.byref(h), 0, 17, 0) == gpuprobe.EINVAL
     assert L.gpu_probe_exchange_create(ctypes.byref(h), 0, 2, 1 << 40) == gpuprobe.ETOOBIG
     assert L.gpu_probe_exchange_status(None) == gpuprobe.ENOTREADY
-    assert L.gpu_probe_allreduce_f32(None, 0, 4, 0, None) == gpuprobe.ENOTREADY
+    assert L.gpu_probe_allreduce_f32(None, 0, 4, 0, 0, None) == gpuprobe.ENOTREADY
     assert L.gpu_probe_checksum_u64_exchange(0x1000, 4, 0, 0x2000, 0x3000, 0, None, None) == gpuprobe.ENOTREADY
     assert L.gpu_probe_exchange_buffer(None) is None and L.gpu_probe_exchange_buffer_bytes(None) == 0
 

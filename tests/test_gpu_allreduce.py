@@ -47,10 +47,10 @@ class Group:
             torch.cuda.synchronize()
             return t.cpu().numpy()
 
-    def allreduce(self, count, offset=0, ctas=None):
+    def allreduce(self, count, offset=0, ctas=None, algo=0):
         for r in range(self.world):
             with torch.cuda.device(self.dev[r]):
-                self.x[r].allreduce_f32(offset, count, self.ctas if ctas is None else ctas, self.st[r].cuda_stream)
+                self.x[r].allreduce_f32(offset, count, self.ctas if ctas is None else ctas, self.st[r].cuda_stream, algo)
 
     def sync(self):
         for d in set(self.dev):
@@ -69,21 +69,31 @@ def rank_order_sum(parts):
     return s
 
 
+ALGOS = {"auto": gpuprobe.ALLREDUCE_AUTO, "pull_push": gpuprobe.ALLREDUCE_PULL_PUSH, "push": gpuprobe.ALLREDUCE_PUSH}
+
+
+@pytest.mark.parametrize("algo", list(ALGOS))
 @pytest.mark.parametrize("world", [1, 2, 3, 4, 8])
-@pytest.mark.parametrize("count", [1, 3, 4, 5, 1023, 4096, 65537, (1 << 20) + 2])
-def test_allreduce_is_the_rank_order_fp32_sum_on_every_rank(world, count):
+@pytest.mark.parametrize("count", [1, 3, 4, 5, 1023, 4096, 65537, 1 << 19, (1 << 20) + 2])
+def test_allreduce_is_the_rank_order_fp32_sum_on_every_rank(world, count, algo):
+    if algo == "push" and (count % 4 or 4 * count > (2 << 20)):
+        pytest.skip("the one-shot algorithm takes whole 16-byte vectors up to 2 MiB")
+    if algo != "pull_push" and count >= (1 << 17) and world > 2 and torch.cuda.device_count() < world:
+        pytest.skip("the one-shot grid must cover the operand; that many CTAs per rank only fit with one GPU per rank")
     rng = np.random.default_rng(100 * world + count % 89)
     parts = [rng.standard_normal(count).astype(np.float32) * np.float32(10.0 ** rng.integers(-3, 4)) for _ in range(world)]
     want = rank_order_sum(parts)
     G = Group(world, 4 * count + 64)
     try:
+        for rep in range(3):  # repeated calls: the one-shot staging is double-buffered by call parity
+            for r in range(world):
+                G.put(r, parts[r])
+            G.allreduce(count, algo=ALGOS[algo])
+            G.sync()
+            for r in range(world):
+                got = G.get(r, count)
+                assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (world, count, algo, rep, r)
         for r in range(world):
-            G.put(r, parts[r])
-        G.allreduce(count)
-        G.sync()
-        for r in range(world):
-            got = G.get(r, count)
-            assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (world, count, r)
             assert G.x[r].status() == 0
     finally:
         G.close()
@@ -147,6 +157,12 @@ def test_allreduce_argument_errors_and_missing_peer():
                 nobuf.allreduce_f32(0, 4)
             assert ei.value.rc == gpuprobe.EINVAL
             nobuf.close()
+            with pytest.raises(gpuprobe.ProbeError) as ei:   # one-shot limits
+                x.allreduce_f32(0, 1022, 0, 0, gpuprobe.ALLREDUCE_PUSH)
+            assert ei.value.rc == gpuprobe.ETOOBIG
+            with pytest.raises(gpuprobe.ProbeError) as ei:
+                x.allreduce_f32(0, 4, 0, 0, 3)
+            assert ei.value.rc == gpuprobe.EINVAL
             x.set_timeout_ms(50)
             x.allreduce_f32(0, 1024, 4, G.st[0].cuda_stream)  # rank 1 never calls
         G.sync()

@@ -80,14 +80,17 @@ class ClockSampler:
            "hw_power_brake_slowdown": 0x80}
     NOTED = {"sw_power_cap": 0x4}
 
-    def __init__(self, index: int, period_s: float = 0.02):
-        self.index, self.period = index, period_s
+    def __init__(self, index: int, period_s: float = 0.02, enabled: bool = True):
+        self.index, self.period, self.enabled = index, period_s, enabled
         self.samples, self.reasons, self.max_mhz = [], set(), None
         self._stop = threading.Event()
         self._thr = None
         self.err = None
 
     def __enter__(self):
+        if not self.enabled:
+            self.err = "disabled (--no-clocks)"
+            return self
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -324,7 +327,7 @@ def run_ours(args, rank, local_rank, world):
     t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     torch.cuda.synchronize()
-    with ClockSampler(local_rank) as clk:
+    with ClockSampler(local_rank, enabled=not args.no_clocks) as clk:
         t_start.record()
         for k in range(args.steps):
             step(evs[k])
@@ -522,10 +525,13 @@ def run_allreduce_sweep(args, torch, dist, world, xchg, st):
     while size <= max_bytes:
         view = buf[: size // 4]
         iters = 20 if size >= (1 << 20) else 50
-        rows_nccl.append(series(lambda: dist.all_reduce(view), size, iters))
+        reps = 3 if size <= (4 << 20) else 1  # short series are noisy: keep the best of three
+        rows_nccl.append(min((series(lambda: dist.all_reduce(view), size, iters) for _ in range(reps)),
+                             key=lambda r: r["us"]))
         buf.fill_(1.0)
         if xchg is not None:
-            rows_own.append(series(lambda: xchg.allreduce_f32(0, size // 4, 0, st), size, iters))
+            rows_own.append(min((series(lambda: xchg.allreduce_f32(0, size // 4, 0, st), size, iters)
+                                 for _ in range(reps)), key=lambda r: r["us"]))
         size <<= 1
     own = None
     if xchg is not None:
@@ -545,8 +551,10 @@ def run_allreduce_sweep(args, torch, dist, world, xchg, st):
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         if int(ok.item()) != 1:
             raise SystemExit(f"bench.py: rank {rank}: gpu_probe_allreduce_f32 result differs from the closed-form sum")
-        own = summary(rows_own, "gpu_probe_allreduce_f32 (K4: one kernel, pull-reduce + push-broadcast over NVLink peer "
-                                "memory), max over ranks")
+        own = summary(rows_own, "gpu_probe_allreduce_f32 (K4, one kernel over NVLink peer memory; AUTO = one-shot push "
+                                "below the threshold, then NVSwitch multimem reduce+broadcast if multicast is "
+                                "available and G >= 3, else pull-reduce + push-broadcast), max over ranks")
+        own["nvswitch_multicast"] = bool(xchg.has_multicast)
         own["checked"] = f"{n_chk} elements against the closed-form sum on every rank"
     if rank != 0:
         return None
@@ -574,6 +582,7 @@ def main():
                     help="N>1: how the 16-byte lanes are summed over ranks (fused P2P exchange, or NCCL)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / parity leg")
+    ap.add_argument("--no-clocks", action="store_true", help="ablation only: do not sample NVML clocks while timing")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3  # timing rule: at least 3 warm-up steps

@@ -140,9 +140,11 @@ int gpu_probe_p2p_copy(void *dst, const void *src, uint64_t bytes, void *stream)
  *   create          [blocking, ALLOCATES the segment] on the current device.
  *   connect_local   ranks living in one process: enables peer access both ways and
  *                   hands raw pointers around.  xs[r] must be rank r.
- *   export / connect_ipc   one process per GPU: export gives this rank's CUDA IPC
- *                   handle; carry all `world` handles (rank order) to every rank by
- *                   any host channel and pass them to connect_ipc.
+ *   export / connect_ipc   one process per GPU: export gives 64 opaque bytes (they name a
+ *                   unix socket of this rank); carry all `world` of them (rank order) to
+ *                   every rank by any host channel and pass them to connect_ipc, which
+ *                   trades the segments' file descriptors over those sockets [blocking;
+ *                   every rank must call it].
  *   status          [blocking] 0, or GPU_PROBE_ETIMEDOUT if some call's wait for a peer
  *                   ran out (default 10 s; the kernel then writes all-ones lanes).
  * Rules: every rank makes the same sequence of *_exchange calls (it is a collective);
@@ -163,6 +165,10 @@ int gpu_probe_exchange_set_timeout_ms(gpu_probe_exchange *x, uint64_t ms);
 int gpu_probe_exchange_status(gpu_probe_exchange *x);
 int gpu_probe_exchange_destroy(gpu_probe_exchange *x);
 
+/* 1 when the connected exchange also holds an NVSwitch multicast mapping of all ranks'
+ * segments (set up by connect_local / connect_ipc when every device and the fabric allow it). */
+int gpu_probe_exchange_has_multicast(gpu_probe_exchange *x);
+
 /* This rank's data buffer inside the segment (device pointer; NULL when buffer_bytes was 0). */
 void *gpu_probe_exchange_buffer(gpu_probe_exchange *x);
 uint64_t gpu_probe_exchange_buffer_bytes(gpu_probe_exchange *x);
@@ -175,13 +181,21 @@ uint64_t gpu_probe_exchange_buffer_bytes(gpu_probe_exchange *x);
  *   PUSH       every rank pushes its whole operand into staging on every peer and adds up
  *              what lands in its own; one NVLink traversal -- the latency algorithm.
  *              Needs count % 4 == 0 and 4*count <= 2 MiB, else GPU_PROBE_ETOOBIG.
- *   AUTO       PUSH below a per-world-size threshold, PULL_PUSH above.
+ *   MULTIMEM   as PULL_PUSH, but reduction and broadcast happen inside the NVSwitch
+ *              (multimem.ld_reduce / multimem.st on the multicast alias of the segments):
+ *              (1 + 1/G) x bytes per direction.  Needs gpu_probe_exchange_has_multicast();
+ *              else GPU_PROBE_ENOTREADY.  The switch picks the summation order, so the
+ *              result may differ from the rank-order sum in the last place (ranks still
+ *              agree with each other bit for bit).
+ *   AUTO       PUSH below a per-world-size threshold; above it MULTIMEM when the exchange
+ *              has multicast and G >= 3, else PULL_PUSH.
  * `ctas` = 0 lets the library size the grid.  Every rank must pass the same count, algo and
  * ctas.  World sizes 1..8.  This is the probe's own collective, timed beside NCCL's
  * allreduce (SURVEY 8d "Allreduce sweep"); same rules as the *_exchange calls above. */
 #define GPU_PROBE_ALLREDUCE_AUTO 0
 #define GPU_PROBE_ALLREDUCE_PULL_PUSH 1
 #define GPU_PROBE_ALLREDUCE_PUSH 2
+#define GPU_PROBE_ALLREDUCE_MULTIMEM 3
 int gpu_probe_allreduce_f32(gpu_probe_exchange *x, uint64_t offset_bytes, uint64_t count,
                             int algo, int ctas, void *stream);
 

@@ -38,6 +38,7 @@ struct AllreduceArgs {
   uint64_t operand_off;   // operand = segment + operand_off (payload offset + caller's offset)
   uint64_t count;         // fp32 elements
   uint64_t stage_bytes;   // one staging slot (one-shot algorithm); staging = segment + kHeaderBytes
+  unsigned char *mc;      // NVSwitch multicast alias of ALL ranks' segments (same layout), or null
 };
 
 __device__ __forceinline__ float4 ld_peer(const float4 *p) {  // system-coherent, never from a stale L1 line
@@ -49,6 +50,18 @@ __device__ __forceinline__ float4 ld_peer(const float4 *p) {  // system-coherent
 __device__ __forceinline__ void st_peer(float4 *p, const float4 &v) {
   asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
                :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+// NVLS: one load returns the sum over every rank's copy (added inside the switch), one store
+// writes every rank's copy.  SASS: LDGMC.E.ADD.F32x4 / STG on a multicast address.
+__device__ __forceinline__ float4 ld_reduce_mc(const float4 *mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_mc(float4 *mc, const float4 &v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+               :: "l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 __device__ __forceinline__ float ld_peer(const float *p) {
   float v;
@@ -149,6 +162,59 @@ allreduce_f32_kernel(const AllreduceArgs a) {
   }
 }
 
+// ---- NVLS variant ----------------------------------------------------------------------
+// Same ownership as above (rank r reduces and re-publishes slice r), but the reduction and
+// the broadcast happen INSIDE the NVSwitch: multimem.ld_reduce pulls one vector and receives
+// the sum of all G copies; multimem.st pushes one vector and the switch writes all G copies.
+// Per direction a GPU now moves (1 + 1/G) x bytes instead of 2(G-1)/G x -- 1.56x less at
+// G = 8 -- so bus bandwidth can exceed the link rate.  The switch's summation order is not
+// ours to choose: ranks still agree bit for bit (one reducer per element), but the value may
+// differ from the rank-order sum in the last place.
+template <int U>
+__global__ void __launch_bounds__(kArThreads)
+allreduce_f32_multimem_kernel(const AllreduceArgs a) {
+  uint64_t *hdr = reinterpret_cast<uint64_t *>(a.seg[a.rank]);
+  __shared__ uint64_t epoch0;
+  if (threadIdx.x == 0) epoch0 = hdr[kCtaEpochOffsetWords + blockIdx.x];
+  __syncthreads();
+  const uint64_t e = epoch0;
+  bool ok = cta_barrier(a, e + 1);
+  if (ok) {
+    const int G = a.world;
+    float4 *mc = reinterpret_cast<float4 *>(a.mc + a.operand_off);
+    const uint64_t nvec = a.count / 4;
+    const uint64_t v_lo = nvec * uint64_t(a.rank) / G, v_hi = nvec * uint64_t(a.rank + 1) / G;
+    const uint64_t tile = uint64_t(kArThreads) * U;
+    for (uint64_t base = v_lo + blockIdx.x * tile; base < v_hi; base += uint64_t(gridDim.x) * tile) {
+      float4 v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const uint64_t i = base + uint64_t(u) * kArThreads + threadIdx.x;
+        if (i < v_hi) v[u] = ld_reduce_mc(mc + i);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const uint64_t i = base + uint64_t(u) * kArThreads + threadIdx.x;
+        if (i < v_hi) st_mc(mc + i, v[u]);
+      }
+    }
+    if (a.rank == G - 1 && blockIdx.x == 0 && threadIdx.x < (a.count & 3)) {  // tail: plain peer loads and stores
+      const uint64_t i = nvec * 4 + threadIdx.x;
+      float s = 0.f;
+      for (int p = 0; p < G; ++p) {
+        const float x = ld_peer(reinterpret_cast<const float *>(a.seg[p] + a.operand_off) + i);
+        s = p == 0 ? x : s + x;
+      }
+      for (int p = 0; p < G; ++p) st_peer(reinterpret_cast<float *>(a.seg[p] + a.operand_off) + i, s);
+    }
+    ok = cta_barrier(a, e + 2);
+  }
+  if (threadIdx.x == 0) {
+    hdr[kCtaEpochOffsetWords + blockIdx.x] = e + 2;
+    if (!ok) hdr[1] = 1;
+  }
+}
+
 // ---- one-shot variant for small operands ---------------------------------------------
 // Latency, not bandwidth, decides below a few MiB, and the pull/push kernel above costs
 // four NVLink traversals (barrier, pull round trip, push, barrier).  Here every rank PUSHES
@@ -174,10 +240,14 @@ allreduce_f32_push_kernel(const AllreduceArgs a) {
     const uint64_t i = (uint64_t(u) * gridDim.x + blockIdx.x) * kArThreads + threadIdx.x;
     if (i < nvec) {
       own[u] = mine_op[i];
+      if (a.mc != nullptr && G > 2) {  // one store, the switch writes slot `rank` on every GPU (mine too: harmless)
+        st_mc(reinterpret_cast<float4 *>(a.mc + slot_set + size_t(a.rank) * a.stage_bytes) + i, own[u]);
+      } else {
 #pragma unroll
-      for (int q = 1; q < G; ++q) {  // start with the next rank: spread the first stores over the links
-        const int p = (a.rank + q) % G;
-        st_peer(reinterpret_cast<float4 *>(a.seg[p] + slot_set + size_t(a.rank) * a.stage_bytes) + i, own[u]);
+        for (int q = 1; q < G; ++q) {  // start with the next rank: spread the first stores over the links
+          const int p = (a.rank + q) % G;
+          st_peer(reinterpret_cast<float4 *>(a.seg[p] + slot_set + size_t(a.rank) * a.stage_bytes) + i, own[u]);
+        }
       }
     }
   }
@@ -211,6 +281,8 @@ template <int G>
 static int launch_allreduce(const AllreduceArgs &a, int algo, unsigned grid, cudaStream_t st) {
   if (algo == GPU_PROBE_ALLREDUCE_PUSH) {
     allreduce_f32_push_kernel<G, kPushU><<<grid, kArThreads, 0, st>>>(a);
+  } else if (algo == GPU_PROBE_ALLREDUCE_MULTIMEM) {
+    allreduce_f32_multimem_kernel<4><<<grid, kArThreads, 0, st>>>(a);
   } else {
     constexpr int U = G <= 2 ? 8 : (G <= 4 ? 4 : 2);  // G*U 16-byte loads in flight per thread
     allreduce_f32_kernel<G, U><<<grid, kArThreads, 0, st>>>(a);
@@ -246,7 +318,8 @@ extern "C" int gpu_probe_allreduce_f32(gpu_probe_exchange *x, uint64_t offset_by
   if (x->buffer_bytes == 0 || (offset_bytes & 15)) return GPU_PROBE_EINVAL;
   if (offset_bytes > x->buffer_bytes || count > (x->buffer_bytes - offset_bytes) / 4) return GPU_PROBE_ETOOBIG;
   if (ctas < 0 || ctas > kMaxCommCtas) return GPU_PROBE_EINVAL;
-  if (algo < GPU_PROBE_ALLREDUCE_AUTO || algo > GPU_PROBE_ALLREDUCE_PUSH) return GPU_PROBE_EINVAL;
+  if (algo < GPU_PROBE_ALLREDUCE_AUTO || algo > GPU_PROBE_ALLREDUCE_MULTIMEM) return GPU_PROBE_EINVAL;
+  if (algo == GPU_PROBE_ALLREDUCE_MULTIMEM && !x->mc_enabled) return GPU_PROBE_ENOTREADY;
   int dev = -1;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return int(e);
@@ -260,6 +333,7 @@ extern "C" int gpu_probe_allreduce_f32(gpu_probe_exchange *x, uint64_t offset_by
   for (int p = 0; p < x->world; ++p) a.seg[p] = reinterpret_cast<unsigned char *>(x->peer[p]);
   a.rank = x->rank; a.world = x->world; a.timeout_ns = x->timeout_ns;
   a.operand_off = x->payload_offset + offset_bytes; a.count = count; a.stage_bytes = x->stage_bytes;
+  a.mc = x->mc_enabled ? x->mc_base : nullptr;
   const uint64_t bytes = 4 * count;
   // The one-shot kernel works on whole 16-byte vectors; the buffer is padded to 256 bytes, so
   // the up-to-3 floats past `count` exist -- but they belong to the caller, so only take the
@@ -267,7 +341,9 @@ extern "C" int gpu_probe_allreduce_f32(gpu_probe_exchange *x, uint64_t offset_by
   const bool push_ok = (count % 4 == 0) && bytes <= x->stage_bytes;
   if (algo == GPU_PROBE_ALLREDUCE_PUSH && !push_ok) return GPU_PROBE_ETOOBIG;
   if (algo == GPU_PROBE_ALLREDUCE_AUTO)
-    algo = (push_ok && bytes <= push_threshold_bytes(x->world)) ? GPU_PROBE_ALLREDUCE_PUSH : GPU_PROBE_ALLREDUCE_PULL_PUSH;
+    algo = (push_ok && bytes <= push_threshold_bytes(x->world)) ? GPU_PROBE_ALLREDUCE_PUSH
+           : (x->mc_enabled && x->world >= 3)                          ? GPU_PROBE_ALLREDUCE_MULTIMEM  // (1+1/G) < 2(G-1)/G from G = 3
+                                                                       : GPU_PROBE_ALLREDUCE_PULL_PUSH;
   // Grid: a function of (count, world, algo, ctas, SM count) only, so every rank picks the
   // same one -- CTA b must exist on every rank.  All CTAs are co-resident (<= 1 per SM).
   unsigned grid;

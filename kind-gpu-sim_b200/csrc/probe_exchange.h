@@ -3,6 +3,7 @@
 #pragma once
 
 #include <cstdint>
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 #include "probe_common.cuh"
@@ -13,12 +14,27 @@ struct gpu_probe_exchange {
   uint32_t magic;
   int device, rank, world;
   bool connected;
-  uint64_t *mailbox;            // this rank's segment (cudaMalloc on `device`): header + payload
+  // This rank's symmetric segment: header + staging + payload, ONE physical allocation made
+  // with the driver's virtual-memory API (cuMemCreate) so that it can be (a) shared with other
+  // processes as a file descriptor and (b) bound into an NVSwitch multicast object.
+  CUmemGenericAllocationHandle mem;
+  size_t seg_bytes;             // physical size (multiple of the allocation and multicast granularity)
+  uint64_t *mailbox;            // = the segment's base address on `device`
   uint64_t buffer_bytes;        // payload size (0: lanes exchange only)
   uint64_t stage_bytes;         // one staging slot of the one-shot allreduce (0 when there is no payload)
   uint64_t payload_offset;      // payload = segment + payload_offset (same on every rank)
-  uint64_t *peer[kMaxRanks];    // every rank's mailbox as addressed from `device`
-  bool ipc_opened[kMaxRanks];   // peer[p] came from cudaIpcOpenMemHandle
+  uint64_t *peer[kMaxRanks];    // every rank's segment as addressed from `device`
+  CUmemGenericAllocationHandle peer_mem[kMaxRanks];  // imported handles (other processes' segments)
+  bool peer_imported[kMaxRanks];
+  // NVSwitch multicast (NVLS): one address that reads/writes ALL ranks' segments at once.
+  bool mc_supported;            // this device can join a multicast object
+  bool mc_enabled;              // multicast address is mapped and every rank has bound its segment
+  int *mc_refs;                 // objects of this process that share mc_mem / mc_base; the last one out frees them
+  CUmemGenericAllocationHandle mc_mem;
+  unsigned char *mc_base;       // multicast alias of the segments (same layout)
+  // one process per GPU: handles travel as file descriptors over a unix datagram socket
+  int sock;
+  char sock_name[40];
   unsigned long long timeout_ns;
 };
 

@@ -24,7 +24,7 @@ VARIANTS = {"auto": VARIANT_AUTO, "ldg128": VARIANT_LDG, "tma": VARIANT_TMA, "ld
 
 EINVAL, EALIGN, ETOOBIG, ENOTREADY, ETIMEDOUT = -100, -101, -102, -103, -104
 EXCHANGE_MAX_RANKS, EXCHANGE_HANDLE_BYTES = 16, 64
-ALLREDUCE_AUTO, ALLREDUCE_PULL_PUSH, ALLREDUCE_PUSH = 0, 1, 2
+ALLREDUCE_AUTO, ALLREDUCE_PULL_PUSH, ALLREDUCE_PUSH, ALLREDUCE_MULTIMEM = 0, 1, 2, 3
 
 _u64 = ctypes.c_uint64
 _vp = ctypes.c_void_p
@@ -76,6 +76,8 @@ def lib() -> ctypes.CDLL:
         L.gpu_probe_exchange_connect_ipc.argtypes = [_vp, ctypes.c_char_p]
         L.gpu_probe_exchange_set_timeout_ms.argtypes = [_vp, _u64]
         L.gpu_probe_exchange_status.argtypes = [_vp]
+        L.gpu_probe_exchange_has_multicast.argtypes = [_vp]
+        L.gpu_probe_exchange_has_multicast.restype = ctypes.c_int
         L.gpu_probe_exchange_destroy.argtypes = [_vp]
         L.gpu_probe_checksum_u64_exchange.argtypes = [_vp, _u64, _u64, _vp, _vp, ctypes.c_int, _vp, _vp]
         L.gpu_probe_triad_checksum_exchange.argtypes = [_vp, _vp, _vp, ctypes.c_double, _u64, _u64, _vp, _vp,
@@ -219,6 +221,10 @@ class Exchange:
 
     def status(self) -> int:
         return int(lib().gpu_probe_exchange_status(self._h))
+
+    @property
+    def has_multicast(self) -> bool:
+        return bool(lib().gpu_probe_exchange_has_multicast(self._h))
 
     def checksum_u64(self, w: int, n: int, first_index: int, out_lanes: int, workspace: int,
                      variant: int = VARIANT_AUTO, stream: int = 0) -> None:

@@ -84,7 +84,7 @@ static void die_usage(const char *fmt, ...) {
           "\nusage: gpu-probe [--expect-gpus=N] [--bytes=B] [--iters=K] [--warmup=W]\n"
           "                 [--variant=auto|ldg128|tma|ldg256] [--max-gpus=N]\n"
           "                 [--sweep-max-bytes=B] [--p2p-bytes=B] [--no-sweep] [--no-p2p] [--no-sharded]\n"
-          "                 [--measured-hbm-gbs=X] [--allreduce-algo=auto|pull_push|push]\n");
+          "                 [--measured-hbm-gbs=X] [--allreduce-algo=auto|pull_push|push|multimem]\n");
   printf("PROBE FAIL rc=%d\n", RC_USAGE);
   exit(RC_USAGE);
 }
@@ -141,6 +141,7 @@ static void parse_options(int argc, char **argv, options *o) {
       if (!strcmp(v, "auto")) o->allreduce_algo = GPU_PROBE_ALLREDUCE_AUTO;
       else if (!strcmp(v, "pull_push")) o->allreduce_algo = GPU_PROBE_ALLREDUCE_PULL_PUSH;
       else if (!strcmp(v, "push")) o->allreduce_algo = GPU_PROBE_ALLREDUCE_PUSH;
+      else if (!strcmp(v, "multimem")) o->allreduce_algo = GPU_PROBE_ALLREDUCE_MULTIMEM;
       else die_usage("--allreduce-algo: unknown algorithm '%s'", v);
     } else if (!strcmp(a, "--no-sweep")) o->do_sweep = 0;
     else if (!strcmp(a, "--no-p2p")) o->do_p2p = 0;
@@ -565,6 +566,13 @@ static int phase_sweep(const options *o, gpu_state *gs, int ng, nccl_api *nc) {
       bufs[d] = (float *)gpu_probe_exchange_buffer(xs[d]);
     }
     PR(gpu_probe_exchange_connect_local(xs, G));
+    for (int d = 0; d < G; ++d) bufs[d] = (float *)gpu_probe_exchange_buffer(xs[d]);
+    printf("PROBE INFO allreduce_group gpus=%d nvswitch_multicast=%d own_algo=%s\n", G,
+           gpu_probe_exchange_has_multicast(xs[0]), o->allreduce_algo_name);
+    if (o->allreduce_algo == GPU_PROBE_ALLREDUCE_MULTIMEM && !gpu_probe_exchange_has_multicast(xs[0])) {
+      fprintf(stderr, "gpu-probe: --allreduce-algo=multimem but this group has no NVSwitch multicast\n");
+      return RC_USAGE;
+    }
     if (nc->so) NC(nc, nc->CommInitAll(comms, G, devs));
 
     for (int use_nccl = nc->so ? 1 : 0; use_nccl >= 0; --use_nccl) {

@@ -23,7 +23,7 @@ def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("gloo")
-    x = gpuprobe.Exchange(rank, world)
+    x = gpuprobe.Exchange(rank, world, 8 << 20)
     handles = [None] * world
     dist.all_gather_object(handles, x.export_handle())
     x.connect_ipc(b"".join(handles))
@@ -54,10 +54,35 @@ def main():
         if got != want or x.status() != 0:
             print(f"rank {rank} call {k}: lanes {got} != oracle {want} (status {x.status()})", flush=True)
             sys.exit(1)
+    # K4 over the same segments: integer-valued operands, so every algorithm must hit the closed form exactly
+    cnt = (1 << 20) + 4
+    algos = [gpuprobe.ALLREDUCE_PULL_PUSH, gpuprobe.ALLREDUCE_AUTO]
+    if x.has_multicast:
+        algos.append(gpuprobe.ALLREDUCE_MULTIMEM)
+    pat = (torch.arange(cnt, device="cuda", dtype=torch.float32) % 7 + 1)
+    for algo in algos + [gpuprobe.ALLREDUCE_PUSH]:
+        n_el = cnt if algo != gpuprobe.ALLREDUCE_PUSH else 1 << 18
+        src = pat[:n_el] * float(rank + 1)
+        gpuprobe.p2p_copy(x.buffer, src.data_ptr(), 4 * n_el, st)
+        torch.cuda.synchronize()
+        dist.barrier()
+        for _ in range(2):
+            x.allreduce_f32(0, n_el, 0, st, algo)
+            outp = torch.empty(n_el, dtype=torch.float32, device="cuda")
+            gpuprobe.p2p_copy(outp.data_ptr(), x.buffer, 4 * n_el, st)
+            torch.cuda.synchronize()
+            scale = float(world * (world + 1) // 2)
+            if not torch.equal(outp, pat[:n_el] * scale) or x.status() != 0:
+                print(f"rank {rank}: allreduce algo {algo} wrong (status {x.status()})", flush=True)
+                sys.exit(1)
+            gpuprobe.p2p_copy(x.buffer, src.data_ptr(), 4 * n_el, st)  # restore the inputs for the second call
+            torch.cuda.synchronize()
+            dist.barrier()
+    mc = x.has_multicast
     dist.barrier()
     x.close()
     if rank == 0:
-        print(f"EXCHANGE_IPC_OK world={world} lanes=0x{want[0]:016x},0x{want[1]:016x}", flush=True)
+        print(f"EXCHANGE_IPC_OK world={world} multicast={int(mc)} lanes=0x{want[0]:016x},0x{want[1]:016x}", flush=True)
     dist.destroy_process_group()
 
 

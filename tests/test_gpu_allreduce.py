@@ -69,7 +69,19 @@ def rank_order_sum(parts):
     return s
 
 
-ALGOS = {"auto": gpuprobe.ALLREDUCE_AUTO, "pull_push": gpuprobe.ALLREDUCE_PULL_PUSH, "push": gpuprobe.ALLREDUCE_PUSH}
+ALGOS = {"auto": gpuprobe.ALLREDUCE_AUTO, "pull_push": gpuprobe.ALLREDUCE_PULL_PUSH, "push": gpuprobe.ALLREDUCE_PUSH,
+         "multimem": gpuprobe.ALLREDUCE_MULTIMEM}
+
+
+def assert_sum(got, parts, want, exact, ctx):
+    """exact: bit-identical to the rank-order fp32 sum.  Otherwise (NVLS: the switch chooses the
+    order) within the worst-case fp32 reordering error of a G-term sum."""
+    if exact:
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), ctx
+        return
+    ref = np.sum(np.stack(parts).astype(np.float64), axis=0)
+    bound = len(parts) * np.finfo(np.float32).eps * np.sum(np.abs(np.stack(parts)).astype(np.float64), axis=0)
+    assert np.all(np.abs(got.astype(np.float64) - ref) <= bound + 1e-30), ctx
 
 
 @pytest.mark.parametrize("algo", list(ALGOS))
@@ -78,21 +90,29 @@ ALGOS = {"auto": gpuprobe.ALLREDUCE_AUTO, "pull_push": gpuprobe.ALLREDUCE_PULL_P
 def test_allreduce_is_the_rank_order_fp32_sum_on_every_rank(world, count, algo):
     if algo == "push" and (count % 4 or 4 * count > (2 << 20)):
         pytest.skip("the one-shot algorithm takes whole 16-byte vectors up to 2 MiB")
-    if algo != "pull_push" and count >= (1 << 17) and world > 2 and torch.cuda.device_count() < world:
+    if algo == "multimem" and torch.cuda.device_count() < max(world, 2):
+        pytest.skip("NVSwitch multicast needs one GPU per rank")
+    if algo not in ("pull_push", "multimem") and count >= (1 << 17) and world > 2 and torch.cuda.device_count() < world:
         pytest.skip("the one-shot grid must cover the operand; that many CTAs per rank only fit with one GPU per rank")
     rng = np.random.default_rng(100 * world + count % 89)
     parts = [rng.standard_normal(count).astype(np.float32) * np.float32(10.0 ** rng.integers(-3, 4)) for _ in range(world)]
     want = rank_order_sum(parts)
     G = Group(world, 4 * count + 64)
     try:
+        if algo == "multimem" and not G.x[0].has_multicast:
+            pytest.skip("this box does not offer NVSwitch multicast")
+        # the switch's summation order is its own: NVLS results are checked within the reordering bound
+        exact = not (G.x[0].has_multicast and (algo == "multimem" or (algo == "auto" and world >= 3)))
         for rep in range(3):  # repeated calls: the one-shot staging is double-buffered by call parity
             for r in range(world):
                 G.put(r, parts[r])
             G.allreduce(count, algo=ALGOS[algo])
             G.sync()
+            first = G.get(0, count)
             for r in range(world):
                 got = G.get(r, count)
-                assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (world, count, algo, rep, r)
+                assert_sum(got, parts, want, exact, (world, count, algo, rep, r))
+                assert np.array_equal(got.view(np.uint32), first.view(np.uint32)), "ranks must agree bit for bit"
         for r in range(world):
             assert G.x[r].status() == 0
     finally:
@@ -161,8 +181,12 @@ def test_allreduce_argument_errors_and_missing_peer():
                 x.allreduce_f32(0, 1022, 0, 0, gpuprobe.ALLREDUCE_PUSH)
             assert ei.value.rc == gpuprobe.ETOOBIG
             with pytest.raises(gpuprobe.ProbeError) as ei:
-                x.allreduce_f32(0, 4, 0, 0, 3)
+                x.allreduce_f32(0, 4, 0, 0, 4)
             assert ei.value.rc == gpuprobe.EINVAL
+            if not x.has_multicast:
+                with pytest.raises(gpuprobe.ProbeError) as ei:
+                    x.allreduce_f32(0, 4, 0, 0, gpuprobe.ALLREDUCE_MULTIMEM)
+                assert ei.value.rc == gpuprobe.ENOTREADY
             x.set_timeout_ms(50)
             x.allreduce_f32(0, 1024, 4, G.st[0].cuda_stream)  # rank 1 never calls
         G.sync()

@@ -21,6 +21,7 @@
 // No reference counterpart (slot: /root/reference/pods/nvidia-gpu-test-pod.yaml:9).
 #include "gpu_probe.h"
 
+#include <cstdlib>
 #include <cstring>
 #include <cuda_runtime.h>
 
@@ -282,7 +283,11 @@ static int launch_allreduce(const AllreduceArgs &a, int algo, unsigned grid, cud
   if (algo == GPU_PROBE_ALLREDUCE_PUSH) {
     allreduce_f32_push_kernel<G, kPushU><<<grid, kArThreads, 0, st>>>(a);
   } else if (algo == GPU_PROBE_ALLREDUCE_MULTIMEM) {
-    allreduce_f32_multimem_kernel<4><<<grid, kArThreads, 0, st>>>(a);
+    static const int u = [] { const char *e = getenv("GPU_PROBE_TUNE_MM_U"); return e ? atoi(e) : 0; }();  // dev knob
+    if (u == 2) allreduce_f32_multimem_kernel<2><<<grid, kArThreads, 0, st>>>(a);
+    else if (u == 8) allreduce_f32_multimem_kernel<8><<<grid, kArThreads, 0, st>>>(a);
+    else if (u == 1) allreduce_f32_multimem_kernel<1><<<grid, kArThreads, 0, st>>>(a);
+    else allreduce_f32_multimem_kernel<4><<<grid, kArThreads, 0, st>>>(a);
   } else {
     constexpr int U = G <= 2 ? 8 : (G <= 4 ? 4 : 2);  // G*U 16-byte loads in flight per thread
     allreduce_f32_kernel<G, U><<<grid, kArThreads, 0, st>>>(a);
@@ -309,7 +314,7 @@ static int device_sms(int dev, int *sms) {
 // operand per GPU instead of 2(G-1)/G x, so the crossover falls as G grows
 // (profiles/allreduce_sweep_r1.md).
 static uint64_t push_threshold_bytes(int world) {
-  return world <= 2 ? (2u << 20) : world <= 4 ? (1u << 20) : (512u << 10);
+  return world <= 4 ? (2u << 20) : (512u << 10);
 }
 
 extern "C" int gpu_probe_allreduce_f32(gpu_probe_exchange *x, uint64_t offset_bytes, uint64_t count, int algo,

@@ -365,7 +365,11 @@ extern "C" int gpu_probe_allreduce_f32(gpu_probe_exchange *x, uint64_t offset_by
     const uint64_t slice_vecs = (count / 4 + x->world - 1) / x->world;
     uint64_t want = (slice_vecs + kArThreads - 1) / kArThreads;  // at least one vector per thread
     if (want < 1) want = 1;
-    grid = ctas > 0 ? unsigned(ctas) : unsigned(want < uint64_t(sms) ? want : uint64_t(sms));
+    // NVLS is bounded by the switch, not by SM issue rate: 16-48 CTAs already reach its ceiling
+    // (835 GB/s bus at 8 GPUs) and more CTAs only add barrier traffic (679 -> 586 GB/s at 64 MiB
+    // going from 16 to 148, profiles/allreduce_tuning_r1.md).  The P2P kernel wants every SM.
+    const uint64_t cap = algo == GPU_PROBE_ALLREDUCE_MULTIMEM ? 32 : uint64_t(sms);
+    grid = ctas > 0 ? unsigned(ctas) : unsigned(want < cap ? want : cap);
     if (grid > unsigned(sms)) grid = unsigned(sms);
   }
   cudaStream_t st = static_cast<cudaStream_t>(stream);

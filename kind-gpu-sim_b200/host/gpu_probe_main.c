@@ -30,6 +30,7 @@
 #define _GNU_SOURCE
 #include <dlfcn.h>
 #include <inttypes.h>
+#include <pthread.h>
 #include <stdarg.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -468,39 +469,68 @@ static int phase_sharded(const options *o, gpu_state *gs, int ng, uint64_t n, nc
 /* ------------- phase C: allreduce sweep at 2/4/8 GPUs -- NCCL and the probe's own K4 */
 /* One timed series: `iters` back-to-back in-place allreduces of S bytes on every GPU of the
  * group, bracketed by events on each GPU's stream; per-iteration time = slowest GPU. */
-static int time_allreduce(const options *o, int use_nccl, nccl_api *nc, ncclComm_t *comms, gpu_state *gs, gpu_probe_exchange **xs,
-                          float **bufs, int G, uint64_t S, int iters, double *ms_out) {
-  int rc;
-  for (int i = -5; i < iters; ++i) {
-    if (i == 0)
-      for (int d = 0; d < G; ++d) {
-        CU(cudaSetDevice(gs[d].dev));
-        CU(cudaEventRecord(gs[d].ev[0], gs[d].st));
-      }
-    if (use_nccl) {
-      NC(nc, nc->GroupStart());
-      for (int d = 0; d < G; ++d)
-        NC(nc, nc->AllReduce(bufs[d], bufs[d], S / 4, ncclFloat, ncclSum, comms[d], gs[d].st));
-      NC(nc, nc->GroupEnd());
-    } else {
-      for (int d = 0; d < G; ++d) {
-        CU(cudaSetDevice(gs[d].dev));
-        PR(gpu_probe_allreduce_f32(xs[d], 0, S / 4, o->allreduce_algo, 0, gs[d].st));
-      }
+/* One host thread per GPU issues that GPU's launches, as one process per GPU would: a single
+ * thread feeding G GPUs makes every small-message figure G launch overheads long. */
+typedef struct {
+  const options *o;
+  int use_nccl, d, G, iters, rc;
+  nccl_api *nc;
+  ncclComm_t comm;
+  gpu_state *g;
+  gpu_probe_exchange *x;
+  float *buf;
+  uint64_t S;
+  pthread_barrier_t *bar;
+  float ms;
+} ar_worker;
+
+static int ar_worker_run(ar_worker *w) {
+  CU(cudaSetDevice(w->g->dev));
+  for (int i = -5; i < w->iters; ++i) {
+    if (i == 0) {
+      CU(cudaStreamSynchronize(w->g->st));
+      pthread_barrier_wait(w->bar); /* all GPUs start the timed series together */
+      CU(cudaEventRecord(w->g->ev[0], w->g->st));
     }
+    if (w->use_nccl) NC(w->nc, w->nc->AllReduce(w->buf, w->buf, w->S / 4, ncclFloat, ncclSum, w->comm, w->g->st));
+    else PR(gpu_probe_allreduce_f32(w->x, 0, w->S / 4, w->o->allreduce_algo, 0, w->g->st));
   }
+  CU(cudaEventRecord(w->g->ev[1], w->g->st));
+  CU(cudaStreamSynchronize(w->g->st));
+  CU(cudaEventElapsedTime(&w->ms, w->g->ev[0], w->g->ev[1]));
+  return 0;
+}
+
+static void *ar_worker_main(void *p) {
+  ar_worker *w = (ar_worker *)p;
+  w->rc = ar_worker_run(w);
+  if (w->rc) { /* do not leave the others waiting at the barrier for ever */
+    fprintf(stderr, "gpu-probe: allreduce worker for gpu %d failed (rc %d); aborting\n", w->g->dev, w->rc);
+    printf("PROBE FAIL rc=%d\n", w->rc);
+    exit(w->rc);
+  }
+  return NULL;
+}
+
+/* One timed series: `iters` back-to-back in-place allreduces of S bytes on every GPU of the
+ * group, bracketed by events on each GPU's stream; per-iteration time = slowest GPU. */
+static int time_allreduce(const options *o, int use_nccl, nccl_api *nc, ncclComm_t *comms, gpu_state *gs,
+                          gpu_probe_exchange **xs, float **bufs, int G, uint64_t S, int iters, double *ms_out) {
+  pthread_t th[MAX_GPUS];
+  ar_worker w[MAX_GPUS];
+  pthread_barrier_t bar;
+  if (pthread_barrier_init(&bar, NULL, (unsigned)G)) return RC_CUDA;
   for (int d = 0; d < G; ++d) {
-    CU(cudaSetDevice(gs[d].dev));
-    CU(cudaEventRecord(gs[d].ev[1], gs[d].st));
+    ar_worker v = {o, use_nccl, d, G, iters, 0, nc, use_nccl ? comms[d] : NULL, &gs[d], xs[d], bufs[d], S, &bar, 0.f};
+    w[d] = v;
+    if (pthread_create(&th[d], NULL, ar_worker_main, &w[d])) return RC_CUDA;
   }
-  if ((rc = sync_all(gs, G))) return rc;
   double ms = 0;
   for (int d = 0; d < G; ++d) {
-    float t;
-    CU(cudaSetDevice(gs[d].dev));
-    CU(cudaEventElapsedTime(&t, gs[d].ev[0], gs[d].ev[1]));
-    if (t / iters > ms) ms = t / iters;
+    pthread_join(th[d], NULL);
+    if (w[d].ms / iters > ms) ms = w[d].ms / iters;
   }
+  pthread_barrier_destroy(&bar);
   *ms_out = ms;
   return 0;
 }

@@ -14,6 +14,7 @@
 
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cuda_runtime.h>
 
 #include "probe_common.cuh"
@@ -361,6 +362,52 @@ copy_vec(uint4 *__restrict__ dst, const uint4 *__restrict__ src, uint64_t nvec, 
     reinterpret_cast<unsigned char *>(dst)[done + threadIdx.x] = reinterpret_cast<const unsigned char *>(src)[done + threadIdx.x];
 }
 
+// K3 as a pure DMA pipeline: one thread per CTA drives the TMA engine -- bulk loads into a ring
+// of shared-memory stages, bulk stores straight back out of them (UBLKCP.S.G / UBLKCP.G.S).
+// No data ever passes through registers; both sides may be peer memory.  Loads lead by S-1
+// tiles; a stage is refilled once the store that drains it has finished READING it
+// (cp.async.bulk.wait_group.read).
+template <int TILE_BYTES, int S>
+__global__ void __launch_bounds__(32)
+copy_tma(unsigned char *__restrict__ dst, const unsigned char *__restrict__ src, uint64_t bytes) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + size_t(S) * TILE_BYTES);
+  const uint64_t ntiles = bytes / TILE_BYTES;
+  const uint64_t my_tiles = ntiles > blockIdx.x ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < S; ++i) tma::mbar_init(&full[i], 1);
+    tma::fence_barrier_init();
+    const uint64_t policy = tma::policy_evict_first();
+    auto load = [&](uint64_t j) {
+      const int st = int(j % S);
+      const uint64_t t = blockIdx.x + j * gridDim.x;
+      tma::mbar_arrive_expect_tx(&full[st], TILE_BYTES);
+      tma::bulk_load(smem_raw + size_t(st) * TILE_BYTES, src + t * TILE_BYTES, TILE_BYTES, &full[st], policy);
+    };
+    for (uint64_t j = 0; j < uint64_t(S - 1) && j < my_tiles; ++j) load(j);
+    for (uint64_t j = 0; j < my_tiles; ++j) {
+      const int st = int(j % S);
+      const uint64_t t = blockIdx.x + j * gridDim.x;
+      tma::mbar_wait(&full[st], uint32_t(j / S) & 1u);
+      tma::bulk_store(dst + t * TILE_BYTES, smem_raw + size_t(st) * TILE_BYTES, TILE_BYTES);
+      tma::bulk_commit();
+      // stage (j-1)%S == (j+S-1)%S is free once store j-1 has read it: refill it with tile j+S-1
+      tma::bulk_wait_read<1>();
+      if (j + S - 1 < my_tiles) load(j + S - 1);
+    }
+    tma::bulk_wait_all<0>();
+  }
+  // remainder [ntiles*TILE, bytes): fewer than one tile, plain accesses by the last CTA
+  if (blockIdx.x == gridDim.x - 1) {
+    const uint64_t done = ntiles * TILE_BYTES;
+    const uint64_t nvec = (bytes - done) / 16;
+    const uint4 *s4 = reinterpret_cast<const uint4 *>(src + done);
+    uint4 *d4 = reinterpret_cast<uint4 *>(dst + done);
+    for (uint64_t k = threadIdx.x; k < nvec; k += 32) d4[k] = s4[k];
+    for (uint64_t k = done + nvec * 16 + threadIdx.x; k < bytes; k += 32) dst[k] = src[k];
+  }
+}
+
 __global__ void __launch_bounds__(kThreads)
 copy_bytes(unsigned char *__restrict__ dst, const unsigned char *__restrict__ src, uint64_t bytes) {
   for (uint64_t k = blockIdx.x * uint64_t(kThreads) + threadIdx.x; k < bytes; k += uint64_t(gridDim.x) * kThreads)
@@ -398,7 +445,7 @@ struct KernelFacts {
 };
 static KernelFacts g_facts[256];
 
-static int kernel_facts(const void *kernel, size_t dyn_smem, int *occ_out, int *sms_out) {
+static int kernel_facts(const void *kernel, size_t dyn_smem, int threads, int *occ_out, int *sms_out) {
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return int(e);
@@ -419,7 +466,7 @@ static int kernel_facts(const void *kernel, size_t dyn_smem, int *occ_out, int *
       e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(dyn_smem));
       if (e != cudaSuccess) return int(e);
     }
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kThreads, dyn_smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, threads, dyn_smem);
     if (e != cudaSuccess) return int(e);
     if (occ < 1) return int(cudaErrorLaunchOutOfResources);
     const void *expect = nullptr;
@@ -438,7 +485,7 @@ static int kernel_facts(const void *kernel, size_t dyn_smem, int *occ_out, int *
 template <typename K>
 static int persistent_grid(K kernel, size_t dyn_smem, uint64_t tiles, unsigned *grid, int max_ctas_per_sm = 0) {
   int sms = 0, occ = 0;
-  int rc = kernel_facts(reinterpret_cast<const void *>(kernel), dyn_smem, &occ, &sms);
+  int rc = kernel_facts(reinterpret_cast<const void *>(kernel), dyn_smem, kThreads, &occ, &sms);
   if (rc) return rc;
   if (max_ctas_per_sm > 0 && occ > max_ctas_per_sm) occ = max_ctas_per_sm;
   uint64_t g = uint64_t(sms) * uint64_t(occ);
@@ -471,6 +518,7 @@ constexpr int kChecksumTile = 4096, kChecksumStages = 4, kChecksumCtasPerSm = 1;
 // LDG geometry from the same sweeps: mixed read/write traffic wants FEW resident CTAs
 // (triad: 2/SM with 8x16 B or 4x32 B loads per array per thread -> 6700 / 6530 GB/s;
 // 8/SM: 6100-6300), read-only wants more (checksum: 6/SM -> 7350 GB/s).
+constexpr int kCopyTileBytes = 32 * 1024, kCopyStages = 3;
 constexpr int kLdgTriadCtasPerSm = 2;
 constexpr int kLdgChecksumCtasPerSm = 6;
 
@@ -646,6 +694,21 @@ int gpu_probe_p2p_copy(void *dst, const void *src, uint64_t bytes, void *stream)
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   unsigned grid = 1;
   int rc;
+  // Large aligned copies: the TMA ring (32 KiB tiles x 3 stages, 1 CTA/SM = 96 KiB in flight per
+  // SM) measured 6470 GB/s locally against 5835 for the LDG/STG kernel; to a peer both sit at the
+  // same 711 GB/s (the copy engine reaches 779), so the choice only matters on the HBM side
+  // (tools/tune_copy.py, profiles/tune_copy_r1.log).  Small copies keep the LDG kernel: a ring
+  // needs a few tiles per CTA to fill.
+  if (aligned(dst, 16) && aligned(src, 16) && bytes >= (uint64_t(8) << 20)) {
+    auto k = copy_tma<kCopyTileBytes, kCopyStages>;
+    constexpr size_t smem = size_t(kCopyTileBytes) * kCopyStages + sizeof(uint64_t) * kCopyStages;
+    int occ = 0, sms = 0;
+    if ((rc = kernel_facts(reinterpret_cast<const void *>(k), smem, 32, &occ, &sms))) return rc;
+    uint64_t g = uint64_t(sms), tiles = bytes / kCopyTileBytes;
+    if (g > tiles) g = tiles;
+    k<<<unsigned(g), 32, smem, st>>>(static_cast<unsigned char *>(dst), static_cast<const unsigned char *>(src), bytes);
+    return launch_rc();
+  }
   if (aligned(dst, 16) && aligned(src, 16)) {
     constexpr int U = 8;
     const uint64_t nvec = bytes / 16;

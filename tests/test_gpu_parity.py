@@ -197,7 +197,9 @@ def test_checksum_is_idempotent_and_stream_ordered():
         assert lanes_of(out) == want
 
 
-@pytest.mark.parametrize("nbytes", [0, 1, 15, 16, 17, 4095, 4096, (1 << 20) + 7, (64 << 20) + 24])
+# below 8 MiB: LDG/STG kernel; from 8 MiB with 16-byte-aligned pointers: TMA ring (32 KiB tiles) + plain tail
+@pytest.mark.parametrize("nbytes", [0, 1, 15, 16, 17, 4095, 4096, (1 << 20) + 7, (8 << 20) - 16, 8 << 20, (8 << 20) + 16,
+                                    (64 << 20) + 24, 148 * 3 * 32768 * 2 + 32768 + 16 + 5])
 def test_copy_kernel_local(nbytes):
     src = torch.randint(0, 256, (nbytes + 64,), dtype=torch.uint8, device="cuda")
     for so, do in ((0, 0), (16, 32), (1, 0), (0, 3)):

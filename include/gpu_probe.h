@@ -212,6 +212,22 @@ int gpu_probe_triad_checksum_exchange(double *a, const double *b, const double *
                                       uint64_t *out_lanes, void *workspace, int variant,
                                       gpu_probe_exchange *x, void *stream);
 
+/* Single-GPU self-test of the multi-GPU protocols.  Ranks that wait for each other must be
+ * resident on the GPU at the same time, and nothing guarantees that for separate launches
+ * on ONE device.  On a box with fewer GPUs than ranks, create all `world` exchanges on the
+ * current device, connect_local them, and use these calls: every rank runs in the rows of
+ * ONE launch (cooperative for the allreduce), executing the same device code as the
+ * per-rank entry points.  Diagnostics, never faster than anything; world <= 8; MULTIMEM is
+ * not available (one device cannot form a multicast group); the allreduce returns
+ * GPU_PROBE_ETOOBIG when world x ctas CTAs cannot be resident together (pass a small ctas).
+ * Array arguments are host arrays of `world` entries, index = rank. */
+int gpu_probe_checksum_u64_exchange_group(const uint64_t *const *w, const uint64_t *n,
+                                          const uint64_t *first_index, uint64_t *const *out_lanes,
+                                          void *const *workspace, gpu_probe_exchange *const *xs,
+                                          int world, void *stream);
+int gpu_probe_allreduce_f32_group(gpu_probe_exchange *const *xs, int world, uint64_t offset_bytes,
+                                  uint64_t count, int algo, int ctas, void *stream);
+
 /* ---- host-buffer pipeline (the end-to-end call for a host that holds b, c) ----
  * create [blocking, ALLOCATES]: device staging for `depth` chunks of
  * `chunk_elems` doubles x3 arrays, two streams, events -- on the current device.

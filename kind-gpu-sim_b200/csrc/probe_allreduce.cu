@@ -131,8 +131,7 @@ __device__ __forceinline__ void reduce_broadcast(const AllreduceArgs &a, uint64_
 }
 
 template <int G, int U>
-__global__ void __launch_bounds__(kArThreads)
-allreduce_f32_kernel(const AllreduceArgs a) {
+__device__ __forceinline__ void pull_push_body(const AllreduceArgs &a) {
   uint64_t *hdr = reinterpret_cast<uint64_t *>(a.seg[a.rank]);
   __shared__ uint64_t epoch0;
   if (threadIdx.x == 0) epoch0 = hdr[kCtaEpochOffsetWords + blockIdx.x];
@@ -162,6 +161,10 @@ allreduce_f32_kernel(const AllreduceArgs a) {
     if (!ok) hdr[1] = 1;  // sticky error flag, read by gpu_probe_exchange_status
   }
 }
+
+template <int G, int U>
+__global__ void __launch_bounds__(kArThreads)
+allreduce_f32_kernel(const AllreduceArgs a) { pull_push_body<G, U>(a); }
 
 // ---- NVLS variant ----------------------------------------------------------------------
 // Same ownership as above (rank r reduces and re-publishes slice r), but the reduction and
@@ -225,8 +228,7 @@ allreduce_f32_multimem_kernel(const AllreduceArgs a) {
 // still agree bit for bit.  Staging is double-buffered by call parity (same argument as the
 // lanes mailbox), so no trailing barrier is needed; peers never read the operand itself.
 template <int G, int U>
-__global__ void __launch_bounds__(kArThreads)
-allreduce_f32_push_kernel(const AllreduceArgs a) {
+__device__ __forceinline__ void push_body(const AllreduceArgs &a) {
   uint64_t *hdr = reinterpret_cast<uint64_t *>(a.seg[a.rank]);
   __shared__ uint64_t epoch0;
   if (threadIdx.x == 0) epoch0 = hdr[kPushEpochOffsetWords + blockIdx.x];
@@ -276,6 +278,26 @@ allreduce_f32_push_kernel(const AllreduceArgs a) {
   }
 }
 
+template <int G, int U>
+__global__ void __launch_bounds__(kArThreads)
+allreduce_f32_push_kernel(const AllreduceArgs a) { push_body<G, U>(a); }
+
+// ---- single-GPU group self-test ---------------------------------------------------------
+// Ranks that wait for each other must be resident at the same time, and nothing guarantees
+// that for SEPARATE launches on one GPU.  To validate the protocols on a box with fewer GPUs
+// than ranks, all G ranks run as ONE cooperative launch: grid = (ctas, G), row y is rank y and
+// executes exactly the bodies above (blockIdx.x / gridDim.x mean the same as in a per-rank
+// launch).  Never faster than anything; a diagnostic.
+struct GroupArgs { AllreduceArgs r[8]; };
+
+template <int G>
+__global__ void __launch_bounds__(kArThreads)
+allreduce_f32_group_kernel(const GroupArgs ga, int algo) {
+  const AllreduceArgs &a = ga.r[blockIdx.y];
+  if (algo == GPU_PROBE_ALLREDUCE_PUSH) push_body<G, 2>(a);
+  else pull_push_body<G, 2>(a);
+}
+
 constexpr int kPushU = 2;  // vectors per thread in the one-shot kernel: grid * 512 * kPushU * 16 B covers the operand
 
 template <int G>
@@ -317,19 +339,23 @@ static uint64_t push_threshold_bytes(int world) {
   return world <= 4 ? (2u << 20) : (512u << 10);
 }
 
-extern "C" int gpu_probe_allreduce_f32(gpu_probe_exchange *x, uint64_t offset_bytes, uint64_t count, int algo,
-                                       int ctas, void *stream) {
+// Argument checks, algorithm choice and grid size for one rank's call.  *count == 0 on return
+// means "nothing to do".  The grid is a function of (count, world, algo, ctas, SM count) only,
+// so every rank picks the same one -- CTA b must exist on every rank.
+static int plan_allreduce(gpu_probe_exchange *x, uint64_t offset_bytes, uint64_t count, int *algo_io, int ctas,
+                          AllreduceArgs *a_out, unsigned *grid_out) {
+  int algo = *algo_io;
   if (!live(x) || !x->connected) return GPU_PROBE_ENOTREADY;
   if (x->buffer_bytes == 0 || (offset_bytes & 15)) return GPU_PROBE_EINVAL;
   if (offset_bytes > x->buffer_bytes || count > (x->buffer_bytes - offset_bytes) / 4) return GPU_PROBE_ETOOBIG;
   if (ctas < 0 || ctas > kMaxCommCtas) return GPU_PROBE_EINVAL;
   if (algo < GPU_PROBE_ALLREDUCE_AUTO || algo > GPU_PROBE_ALLREDUCE_MULTIMEM) return GPU_PROBE_EINVAL;
   if (algo == GPU_PROBE_ALLREDUCE_MULTIMEM && !x->mc_enabled) return GPU_PROBE_ENOTREADY;
+  if (x->world > 8) return GPU_PROBE_EINVAL;  // more than 8 ranks: not one NVSwitch domain of this probe
   int dev = -1;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return int(e);
   if (dev != x->device) return GPU_PROBE_EINVAL;
-  if (count == 0) return 0;  // every rank passes the same count, so every rank skips
   int sms = 0;
   int rc = device_sms(dev, &sms);
   if (rc) return rc;
@@ -349,8 +375,6 @@ extern "C" int gpu_probe_allreduce_f32(gpu_probe_exchange *x, uint64_t offset_by
     algo = (push_ok && bytes <= push_threshold_bytes(x->world)) ? GPU_PROBE_ALLREDUCE_PUSH
            : (x->mc_enabled && x->world >= 3)                          ? GPU_PROBE_ALLREDUCE_MULTIMEM  // (1+1/G) < 2(G-1)/G from G = 3
                                                                        : GPU_PROBE_ALLREDUCE_PULL_PUSH;
-  // Grid: a function of (count, world, algo, ctas, SM count) only, so every rank picks the
-  // same one -- CTA b must exist on every rank.  All CTAs are co-resident (<= 1 per SM).
   unsigned grid;
   if (algo == GPU_PROBE_ALLREDUCE_PUSH) {
     const uint64_t nvec = count / 4;
@@ -360,6 +384,7 @@ extern "C" int gpu_probe_allreduce_f32(gpu_probe_exchange *x, uint64_t offset_by
     if (g > uint64_t(sms)) g = uint64_t(sms);
     if (ctas > 0) g = uint64_t(ctas);
     if (g < need) g = need;
+    if (g < 1) g = 1;
     grid = unsigned(g);
   } else {
     const uint64_t slice_vecs = (count / 4 + x->world - 1) / x->world;
@@ -372,6 +397,19 @@ extern "C" int gpu_probe_allreduce_f32(gpu_probe_exchange *x, uint64_t offset_by
     grid = ctas > 0 ? unsigned(ctas) : unsigned(want < cap ? want : cap);
     if (grid > unsigned(sms)) grid = unsigned(sms);
   }
+  *algo_io = algo;
+  *a_out = a;
+  *grid_out = grid;
+  return 0;
+}
+
+extern "C" int gpu_probe_allreduce_f32(gpu_probe_exchange *x, uint64_t offset_bytes, uint64_t count, int algo,
+                                       int ctas, void *stream) {
+  AllreduceArgs a;
+  unsigned grid = 1;
+  int rc = plan_allreduce(x, offset_bytes, count, &algo, ctas, &a, &grid);
+  if (rc) return rc;
+  if (count == 0) return 0;  // every rank passes the same count, so every rank skips
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (x->world) {
     case 1: return launch_allreduce<1>(a, algo, grid, st);
@@ -381,7 +419,52 @@ extern "C" int gpu_probe_allreduce_f32(gpu_probe_exchange *x, uint64_t offset_by
     case 5: return launch_allreduce<5>(a, algo, grid, st);
     case 6: return launch_allreduce<6>(a, algo, grid, st);
     case 7: return launch_allreduce<7>(a, algo, grid, st);
-    case 8: return launch_allreduce<8>(a, algo, grid, st);
-    default: return GPU_PROBE_EINVAL;  // more than 8 ranks: not one NVSwitch domain of this probe
+    default: return launch_allreduce<8>(a, algo, grid, st);
+  }
+}
+
+template <int G>
+static int launch_group(const GroupArgs &ga, int algo, unsigned grid, cudaStream_t st) {
+  auto k = allreduce_f32_group_kernel<G>;
+  int per_sm = 0, dev = 0, sms = 0;
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kArThreads, 0);
+  if (e == cudaSuccess) e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return int(e);
+  int rc = device_sms(dev, &sms);
+  if (rc) return rc;
+  if (uint64_t(grid) * G > uint64_t(per_sm) * sms) return GPU_PROBE_ETOOBIG;  // all ranks' CTAs must be resident together
+  void *params[] = {const_cast<GroupArgs *>(&ga), &algo};
+  e = cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(k), dim3(grid, G), dim3(kArThreads), params, 0, st);
+  return int(e);
+}
+
+extern "C" int gpu_probe_allreduce_f32_group(gpu_probe_exchange *const *xs, int world, uint64_t offset_bytes,
+                                             uint64_t count, int algo, int ctas, void *stream) {
+  if (!xs || world < 1 || world > 8) return GPU_PROBE_EINVAL;
+  if (algo == GPU_PROBE_ALLREDUCE_MULTIMEM) return GPU_PROBE_EINVAL;  // one device cannot form a multicast group
+  GroupArgs ga;
+  unsigned grid = 1;
+  int algo0 = algo;
+  for (int r = 0; r < world; ++r) {
+    if (!live(xs[r])) return GPU_PROBE_ENOTREADY;
+    if (xs[r]->world != world || xs[r]->rank != r) return GPU_PROBE_EINVAL;
+    int algo_r = algo;
+    unsigned grid_r = 1;
+    int rc = plan_allreduce(xs[r], offset_bytes, count, &algo_r, ctas, &ga.r[r], &grid_r);  // also checks: all on the current device
+    if (rc) return rc;
+    if (r == 0) { algo0 = algo_r; grid = grid_r; }
+    else if (algo_r != algo0 || grid_r != grid) return GPU_PROBE_EINVAL;
+  }
+  if (count == 0) return 0;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (world) {
+    case 1: return launch_group<1>(ga, algo0, grid, st);
+    case 2: return launch_group<2>(ga, algo0, grid, st);
+    case 3: return launch_group<3>(ga, algo0, grid, st);
+    case 4: return launch_group<4>(ga, algo0, grid, st);
+    case 5: return launch_group<5>(ga, algo0, grid, st);
+    case 6: return launch_group<6>(ga, algo0, grid, st);
+    case 7: return launch_group<7>(ga, algo0, grid, st);
+    default: return launch_group<8>(ga, algo0, grid, st);
   }
 }

@@ -225,25 +225,28 @@ __device__ __forceinline__ void exchange_lanes(uint64_t s0, uint64_t s1, const E
 // Wrapping u64 sums are associative and commutative, so the order CTAs (or GPUs)
 // finish in cannot change a bit.
 //   lane1 was accumulated with LOCAL indices k; sum w*(2(f+k)+1) = lane1 + 2f*lane0.
-__device__ __forceinline__ void finish_lanes(Lanes mine, uint64_t first_index,
-                                             uint64_t *__restrict__ out,
-                                             uint64_t *__restrict__ ws, uint64_t *smem,
-                                             const ExchangeArgs &x) {
+// `cta` / `nctas`: this CTA's index and the CTA count of ITS RANK -- blockIdx.x / gridDim.x in
+// the product kernels (one rank per launch); the single-GPU group self-test runs several ranks
+// in one launch and passes blockIdx.x / gridDim.x of the rank's row of the grid.
+__device__ __forceinline__ void finish_lanes_at(Lanes mine, uint64_t first_index,
+                                                uint64_t *__restrict__ out,
+                                                uint64_t *__restrict__ ws, uint64_t *smem,
+                                                const ExchangeArgs &x, unsigned cta, unsigned nctas) {
   __shared__ bool is_last;
   Lanes blk = block_sum(mine, smem);
   if (threadIdx.x == 0) {
-    uint64_t *part = ws + kPartialsOffsetWords + 2 * size_t(blockIdx.x);
+    uint64_t *part = ws + kPartialsOffsetWords + 2 * size_t(cta);
     __stcg(part, blk.s0);
     __stcg(part + 1, blk.s1);
     __threadfence();
     unsigned long long t = atomicAdd(reinterpret_cast<unsigned long long *>(ws), 1ull);
-    is_last = (t == gridDim.x - 1);
+    is_last = (t == nctas - 1);
   }
   __syncthreads();
   if (!is_last) return;
   __threadfence();
   Lanes acc{0, 0};
-  for (unsigned i = threadIdx.x; i < gridDim.x; i += blockDim.x) {
+  for (unsigned i = threadIdx.x; i < nctas; i += blockDim.x) {
     const uint64_t *part = ws + kPartialsOffsetWords + 2 * size_t(i);
     acc.s0 += __ldcg(part);
     acc.s1 += __ldcg(part + 1);
@@ -257,6 +260,13 @@ __device__ __forceinline__ void finish_lanes(Lanes mine, uint64_t first_index,
     out[0] = l0;
     out[1] = l1;
   }
+}
+
+__device__ __forceinline__ void finish_lanes(Lanes mine, uint64_t first_index,
+                                             uint64_t *__restrict__ out,
+                                             uint64_t *__restrict__ ws, uint64_t *smem,
+                                             const ExchangeArgs &x) {
+  finish_lanes_at(mine, first_index, out, ws, smem, x, blockIdx.x, gridDim.x);
 }
 
 }  // namespace probe

@@ -632,3 +632,21 @@ extern "C" int gpu_probe_triad_checksum_exchange(double *a_out, const double *b,
   if (rc) return rc;
   return checked_triad_checksum(a_out, b, c, s, n, first_index, out_lanes, workspace, variant, stream, a);
 }
+
+extern "C" int gpu_probe_checksum_u64_exchange_group(const uint64_t *const *w, const uint64_t *n,
+                                                     const uint64_t *first_index, uint64_t *const *out_lanes,
+                                                     void *const *workspace, gpu_probe_exchange *const *xs, int world,
+                                                     void *stream) {
+  if (!w || !n || !first_index || !out_lanes || !workspace || !xs || world < 1 || world > 8) return GPU_PROBE_EINVAL;
+  ChecksumGroupArgs g;
+  std::memset(&g, 0, sizeof(g));
+  for (int r = 0; r < world; ++r) {
+    if (!live(xs[r])) return GPU_PROBE_ENOTREADY;
+    if (xs[r]->world != world || xs[r]->rank != r) return GPU_PROBE_EINVAL;
+    int rc = exchange_args(xs[r], &g.x[r]);  // also checks: connected, and on the current device
+    if (rc) return rc;
+    g.w[r] = w[r]; g.n[r] = n[r]; g.first[r] = first_index[r];
+    g.out[r] = out_lanes[r]; g.ws[r] = static_cast<uint64_t *>(workspace[r]);
+  }
+  return checked_checksum_group(g, world, stream);
+}

@@ -191,6 +191,22 @@ checksum_scalar(const uint64_t *__restrict__ w, uint64_t n, uint64_t first, uint
   finish_lanes(acc, first, out, ws, red, x);
 }
 
+// Single-GPU group self-test (see probe_allreduce.cu): all ranks of a group that lives on ONE
+// device in one launch, grid = (ctas, G); row y is rank y and runs the scalar checksum body,
+// whose tail (finish_lanes -> exchange_lanes) is the code every product variant shares.
+// At most G CTAs ever spin (each rank's last one), so the rows always make progress.
+__global__ void __launch_bounds__(kThreads)
+checksum_group_kernel(const ChecksumGroupArgs g) {
+  __shared__ uint64_t red[64];
+  const int r = blockIdx.y;
+  const uint64_t *__restrict__ w = g.w[r];
+  const uint64_t n = g.n[r];
+  Lanes acc{0, 0};
+  for (uint64_t k = blockIdx.x * uint64_t(kThreads) + threadIdx.x; k < n; k += uint64_t(gridDim.x) * kThreads)
+    acc.add(w[k], 2 * k + 1);
+  finish_lanes(acc, g.first[r], g.out[r], g.ws[r], red, g.x[r]);
+}
+
 // ---------------------------------------------------------------------------
 // TMA variants.  Persistent CTAs; CTA x owns tiles x, x+grid, x+2*grid, ...
 // Stage ring of S slots filled by 1-D bulk copies; slot j%S completes on its own
@@ -603,6 +619,23 @@ int checked_checksum(const uint64_t *w, uint64_t n, uint64_t first_index, uint64
   const uint64_t nvec = n / 2;
   if ((rc = persistent_grid(k, 0, (nvec + kThreads * U - 1) / (kThreads * U), &grid, kLdgChecksumCtasPerSm))) return rc;
   k<<<grid, kThreads, 0, st>>>(reinterpret_cast<const u64x2 *>(w), nvec, n, first_index, out_lanes, ws, x);
+  return launch_rc();
+}
+
+int checked_checksum_group(const ChecksumGroupArgs &g, int world, void *stream) {
+  uint64_t most = 0;
+  for (int r = 0; r < world; ++r) {
+    if (!g.out[r] || !g.ws[r] || (!g.w[r] && g.n[r])) return GPU_PROBE_EINVAL;
+    if (!aligned(g.w[r], 8) || !aligned(g.out[r], 8) || !aligned(g.ws[r], 8)) return GPU_PROBE_EALIGN;
+    if (g.n[r] > most) most = g.n[r];
+  }
+  int sms = 0;
+  int rc = current_device_sms(&sms);
+  if (rc) return rc;
+  uint64_t ctas = (most + kThreads - 1) / kThreads;
+  if (ctas > uint64_t(sms)) ctas = uint64_t(sms);
+  if (ctas < 1) ctas = 1;
+  checksum_group_kernel<<<dim3(unsigned(ctas), unsigned(world)), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(g);
   return launch_rc();
 }
 

@@ -17,4 +17,13 @@ PROBE_INTERNAL int checked_triad_checksum(double *a, const double *b, const doub
                                           uint64_t first_index, uint64_t *out_lanes, void *workspace, int variant,
                                           void *stream, const ExchangeArgs &x);
 
+// Single-GPU group self-test: every rank's checksum + lanes exchange in one launch.
+struct ChecksumGroupArgs {
+  const uint64_t *w[8];
+  uint64_t n[8], first[8];
+  uint64_t *out[8], *ws[8];
+  ExchangeArgs x[8];
+};
+PROBE_INTERNAL int checked_checksum_group(const ChecksumGroupArgs &g, int world, void *stream);
+
 }  // namespace probe

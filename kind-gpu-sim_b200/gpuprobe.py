@@ -82,6 +82,13 @@ def lib() -> ctypes.CDLL:
         L.gpu_probe_checksum_u64_exchange.argtypes = [_vp, _u64, _u64, _vp, _vp, ctypes.c_int, _vp, _vp]
         L.gpu_probe_triad_checksum_exchange.argtypes = [_vp, _vp, _vp, ctypes.c_double, _u64, _u64, _vp, _vp,
                                                         ctypes.c_int, _vp, _vp]
+        L.gpu_probe_checksum_u64_exchange_group.argtypes = [ctypes.POINTER(_vp), ctypes.POINTER(_u64), ctypes.POINTER(_u64),
+                                                            ctypes.POINTER(_vp), ctypes.POINTER(_vp), ctypes.POINTER(_vp),
+                                                            ctypes.c_int, _vp]
+        L.gpu_probe_checksum_u64_exchange_group.restype = ctypes.c_int
+        L.gpu_probe_allreduce_f32_group.argtypes = [ctypes.POINTER(_vp), ctypes.c_int, _u64, _u64, ctypes.c_int,
+                                                    ctypes.c_int, _vp]
+        L.gpu_probe_allreduce_f32_group.restype = ctypes.c_int
         for name in ("gpu_probe_exchange_create", "gpu_probe_exchange_connect_local", "gpu_probe_exchange_export",
                      "gpu_probe_exchange_connect_ipc", "gpu_probe_exchange_set_timeout_ms", "gpu_probe_exchange_status",
                      "gpu_probe_exchange_destroy", "gpu_probe_checksum_u64_exchange",
@@ -205,6 +212,22 @@ class Exchange:
     def connect_local(xs: "list[Exchange]") -> None:
         arr = (_vp * len(xs))(*[x._h for x in xs])
         _check(lib().gpu_probe_exchange_connect_local(arr, len(xs)), "gpu_probe_exchange_connect_local")
+
+    @staticmethod
+    def checksum_u64_group(xs: "list[Exchange]", w: "list[int]", n: "list[int]", first_index: "list[int]",
+                           out_lanes: "list[int]", workspace: "list[int]", stream: int = 0) -> None:
+        """All ranks (exchanges on ONE device) in one launch: the single-GPU self-test form."""
+        g = len(xs)
+        _check(lib().gpu_probe_checksum_u64_exchange_group(
+            (_vp * g)(*w), (_u64 * g)(*n), (_u64 * g)(*[f & (2**64 - 1) for f in first_index]), (_vp * g)(*out_lanes),
+            (_vp * g)(*workspace), (_vp * g)(*[x._h for x in xs]), g, stream), "gpu_probe_checksum_u64_exchange_group")
+
+    @staticmethod
+    def allreduce_f32_group(xs: "list[Exchange]", offset_bytes: int, count: int, ctas: int = 0, stream: int = 0,
+                            algo: int = 0) -> None:
+        g = len(xs)
+        _check(lib().gpu_probe_allreduce_f32_group((_vp * g)(*[x._h for x in xs]), g, offset_bytes, count, algo, ctas,
+                                                   stream), "gpu_probe_allreduce_f32_group")
 
     def export_handle(self) -> bytes:
         buf = ctypes.create_string_buffer(EXCHANGE_HANDLE_BYTES)

@@ -3,8 +3,10 @@ the C ABI.  The result is defined exactly: every element is the fp32 sum of the 
 values taken in rank order 0..G-1, and all ranks hold identical bits -- so the comparison
 with the numpy restatement below is bit-exact, no tolerance.
 
-On a 1-GPU box the ranks share cuda:0 (each on its own stream, few CTAs each so that all of
-them are resident together); with more GPUs the same tests cross NVLink."""
+With one GPU per rank the tests launch one kernel per rank and cross NVLink.  With fewer
+GPUs than ranks all ranks live on cuda:0 and run as the rows of ONE cooperative launch
+(gpu_probe_allreduce_f32_group): kernels that wait for each other are never separate
+launches on one GPU."""
 import numpy as np
 import pytest
 import torch
@@ -15,14 +17,13 @@ pytestmark = pytest.mark.gpu
 
 
 def _devices(world):
-    g = torch.cuda.device_count()
-    return [r % g for r in range(world)] if g < world else list(range(world))
+    return list(range(world)) if torch.cuda.device_count() >= world else [0] * world
 
 
 class Group:
     def __init__(self, world, buffer_bytes):
         self.world, self.dev = world, _devices(world)
-        self.shared = len(set(self.dev)) < world
+        self.shared = world > 1 and len(set(self.dev)) == 1
         self.x, self.st = [], []
         for r in range(world):
             with torch.cuda.device(self.dev[r]):
@@ -32,7 +33,7 @@ class Group:
 
     @property
     def ctas(self):
-        return 8 if self.shared else 0  # shared device: every rank's CTAs must fit on the one GPU together
+        return 8 if self.shared else 0  # shared GPU: world x ctas CTAs must be resident together
 
     def put(self, r, arr, offset=0):
         with torch.cuda.device(self.dev[r]):
@@ -48,6 +49,11 @@ class Group:
             return t.cpu().numpy()
 
     def allreduce(self, count, offset=0, ctas=None, algo=0):
+        if self.shared:  # all ranks in one cooperative launch; few CTAs per rank so that all are resident
+            with torch.cuda.device(0):
+                gpuprobe.Exchange.allreduce_f32_group(self.x, offset, count, self.ctas if ctas is None else ctas,
+                                                      self.st[0].cuda_stream, algo)
+            return
         for r in range(self.world):
             with torch.cuda.device(self.dev[r]):
                 self.x[r].allreduce_f32(offset, count, self.ctas if ctas is None else ctas, self.st[r].cuda_stream, algo)

@@ -1,10 +1,12 @@
 """The checksum fused with its collective (gpu_probe_*_exchange), through the C ABI.
 
 Every rank must end with the lanes of the WHOLE buffer, bit-exact against the CPU
-oracle -- the same bar as the single-GPU checksum.  On a 1-GPU box the protocol is still
-exercised with several ranks that share the one device (each on its own stream); with
-two or more GPUs the same tests run across real peers over NVLink, in one process
-(connect_local) and in one process per GPU (CUDA IPC handles carried over gloo)."""
+oracle -- the same bar as the single-GPU checksum.  With one GPU per rank the tests launch
+one kernel per rank and cross NVLink, in one process (connect_local) and in one process
+per GPU (file descriptors over unix sockets, handles carried over gloo).  With fewer GPUs
+than ranks, kernels that wait for each other must not be separate launches (nothing makes
+them run at the same time), so all ranks live on cuda:0 and run as the rows of ONE launch
+(gpu_probe_checksum_u64_exchange_group): same device code, same mailbox protocol."""
 import os
 import subprocess
 import sys
@@ -24,9 +26,8 @@ ALL_ONES = ((1 << 64) - 1, (1 << 64) - 1)
 
 
 def _devices(world: int) -> list[int]:
-    """Rank -> device: distinct GPUs when the box has them, else everyone on cuda:0."""
-    g = torch.cuda.device_count()
-    return [r % g for r in range(world)] if g < world else list(range(world))
+    """Rank -> device: one GPU per rank when the box has them, else everyone on cuda:0."""
+    return list(range(world)) if torch.cuda.device_count() >= world else [0] * world
 
 
 class Ranks:
@@ -42,6 +43,19 @@ class Ranks:
                 self.ws.append(workspace())
                 self.out.append(lanes_buf())
         gpuprobe.Exchange.connect_local(self.x)
+        self.grouped = world > 1 and len(set(self.dev)) == 1
+
+    def checksum(self, ptrs, ns, firsts, outs):
+        """One sharded checksum + exchange: a launch per rank, or (shared GPU) all ranks in one launch."""
+        if self.grouped:
+            with torch.cuda.device(0):
+                gpuprobe.Exchange.checksum_u64_group(self.x, ptrs, ns, firsts, [o.data_ptr() for o in outs],
+                                                     [w.data_ptr() for w in self.ws], self.st[0].cuda_stream)
+            return
+        for r in range(self.world):
+            with torch.cuda.device(self.dev[r]):
+                self.x[r].checksum_u64(ptrs[r], ns[r], firsts[r], outs[r].data_ptr(), self.ws[r].data_ptr(),
+                                       gpuprobe.VARIANT_AUTO, self.st[r].cuda_stream)
 
     def sync(self):
         for d in set(self.dev):
@@ -77,10 +91,7 @@ def test_sharded_checksum_exchange_matches_oracle(world, n):
                     ts.append(from_np(w[lo:hi]))
                     R.out[r].fill_(-1)
             R.sync()
-            for r, (lo, hi) in enumerate(parts):
-                with torch.cuda.device(R.dev[r]):
-                    R.x[r].checksum_u64(ts[r].data_ptr(), hi - lo, first + lo, R.out[r].data_ptr(),
-                                        R.ws[r].data_ptr(), gpuprobe.VARIANT_AUTO, R.st[r].cuda_stream)
+            R.checksum([t.data_ptr() for t in ts], [hi - lo for lo, hi in parts], [first + lo for lo, _ in parts], R.out)
             R.sync()
             for r in range(world):
                 assert lanes_of(R.out[r]) == want, (world, n, rep, r)
@@ -107,8 +118,15 @@ def test_fused_triad_checksum_exchange_matches_oracle(world, variant):
                 s = R.st[r].cuda_stream
                 gpuprobe.init_fill(b.data_ptr(), m, first + lo, gpuprobe.SEED_B, s)
                 gpuprobe.init_fill(c.data_ptr(), m, first + lo, gpuprobe.SEED_C, s)
-                R.x[r].triad_checksum(a.data_ptr(), b.data_ptr(), c.data_ptr(), gpuprobe.SCALAR, m, first + lo,
-                                      R.out[r].data_ptr(), R.ws[r].data_ptr(), variant, s)
+                if R.grouped:  # shared GPU: triad per rank now, every rank's checksum + exchange in one launch below
+                    gpuprobe.triad(a.data_ptr(), b.data_ptr(), c.data_ptr(), gpuprobe.SCALAR, m, variant, s)
+                else:
+                    R.x[r].triad_checksum(a.data_ptr(), b.data_ptr(), c.data_ptr(), gpuprobe.SCALAR, m, first + lo,
+                                          R.out[r].data_ptr(), R.ws[r].data_ptr(), variant, s)
+        if R.grouped:
+            R.sync()
+            R.checksum([bufs[r][0].data_ptr() for r in range(world)], [hi - lo for lo, hi in parts],
+                       [first + lo for lo, _ in parts], R.out)
         R.sync()
         for r in range(world):
             assert lanes_of(R.out[r]) == want, (world, variant, r)
@@ -132,10 +150,8 @@ def test_exchange_many_calls_in_a_row_stay_in_step():
         outs = [[torch.zeros(2, dtype=torch.int64, device=f"cuda:{R.dev[r]}") for _ in range(200)] for r in range(world)]
         R.sync()
         for k in range(200):
-            for r, (lo, hi) in enumerate(parts):
-                with torch.cuda.device(R.dev[r]):
-                    R.x[r].checksum_u64(ts[r].data_ptr(), hi - lo, lo, outs[r][k].data_ptr(), R.ws[r].data_ptr(),
-                                        gpuprobe.VARIANT_AUTO, R.st[r].cuda_stream)
+            R.checksum([t.data_ptr() for t in ts], [hi - lo for lo, hi in parts], [lo for lo, _ in parts],
+                       [outs[r][k] for r in range(world)])
         R.sync()
         for r in range(world):
             for k in range(200):

@@ -28,5 +28,20 @@ for v in (2, 0, 1):
         gpuprobe.checksum_u64(a.data_ptr(), n, 0, out.data_ptr(), ws.data_ptr(), v, st)
 for _ in range(2):
     gpuprobe.triad_checksum(a.data_ptr(), b.data_ptr(), c.data_ptr(), 3.0, n, 0, out.data_ptr(), ws.data_ptr(), 1, st)
+# K3: large aligned copy -> TMA ring; small -> LDG/STG kernel
+for _ in range(2):
+    gpuprobe.p2p_copy(a.data_ptr(), b.data_ptr(), 8 * n, st)
+for _ in range(2):
+    gpuprobe.p2p_copy(a.data_ptr(), b.data_ptr(), 4 << 20, st)
+# the checksum with the lanes exchange attached (world 1: the mailbox protocol against itself)
+x = gpuprobe.Exchange(0, 1, 256 << 20)
+for _ in range(2):
+    x.checksum_u64(a.data_ptr(), n, 0, out.data_ptr(), ws.data_ptr(), 1, st)
+# K4 on one rank (degenerate traffic, same instruction stream): pull/push and one-shot
+for _ in range(2):
+    x.allreduce_f32(0, (256 << 20) // 4, 0, st, gpuprobe.ALLREDUCE_PULL_PUSH)
+for _ in range(2):
+    x.allreduce_f32(0, (2 << 20) // 4, 0, st, gpuprobe.ALLREDUCE_PUSH)
 torch.cuda.synchronize()
+x.close()
 print("lanes", [hex(int(x) & (2**64 - 1)) for x in out.cpu()])

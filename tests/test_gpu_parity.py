@@ -225,3 +225,35 @@ def test_host_pipeline_matches_oracle(n, chunk, depth, want_a):
             if want_a and n:
                 want = oracle.triad(b.numpy(), c.numpy(), 3.0)
                 assert np.array_equal(a.numpy().view(np.uint64), want.view(np.uint64))
+
+
+def test_beyond_2_32_elements_matches_golden(golden):
+    """Maximum size: 2^32 elements per array (3 x 32 GiB), so every tile, vector and word index in
+    the kernels crosses 32 bits.  Known answer: the golden lanes of 2^32 elements."""
+    n = 1 << 32
+    torch.cuda.empty_cache()
+    free, _ = torch.cuda.mem_get_info()
+    if free < 3 * 8 * n + (4 << 30):
+        pytest.skip(f"needs {3 * 8 * n >> 30} GiB of free HBM, have {free >> 30}")
+    want = tuple(int(v, 16) for v in golden["pow2_lanes"][32])
+    b = torch.empty(n, dtype=torch.float64, device="cuda")
+    c = torch.empty(n, dtype=torch.float64, device="cuda")
+    a = torch.empty(n, dtype=torch.float64, device="cuda")
+    ws, out = workspace(), lanes_buf()
+    gpuprobe.init_fill(b.data_ptr(), n, 0, gpuprobe.SEED_B, stream())
+    gpuprobe.init_fill(c.data_ptr(), n, 0, gpuprobe.SEED_C, stream())
+    gpuprobe.triad_checksum(a.data_ptr(), b.data_ptr(), c.data_ptr(), gpuprobe.SCALAR, n, 0, out.data_ptr(),
+                            ws.data_ptr(), gpuprobe.VARIANT_TMA, stream())
+    torch.cuda.synchronize()
+    assert lanes_of(out) == want, hx(lanes_of(out))
+    for variant in (gpuprobe.VARIANT_LDG, gpuprobe.VARIANT_LDG256, gpuprobe.VARIANT_TMA):
+        a.zero_()
+        gpuprobe.triad(a.data_ptr(), b.data_ptr(), c.data_ptr(), gpuprobe.SCALAR, n, variant, stream())
+        assert gpu_checksum(a, 0, variant, ws) == want, variant
+    # the upper half alone, addressed by its global index: lanes(whole) - lanes(lower half) mod 2^64
+    lower = tuple(int(v, 16) for v in golden["pow2_lanes"][31])
+    half = n // 2
+    got = gpu_checksum(a[half:], half, gpuprobe.VARIANT_AUTO, ws)
+    assert got == ((want[0] - lower[0]) & M64, (want[1] - lower[1]) & M64)
+    del a, b, c
+    torch.cuda.empty_cache()

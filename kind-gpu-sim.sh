@@ -179,6 +179,9 @@ prepare_real_worker() {
       curl -fsSL https://nvidia.github.io/libnvidia-container/stable/deb/nvidia-container-toolkit.list |
         sed "s#deb https://#deb [signed-by=/usr/share/keyrings/nvidia-container-toolkit-keyring.gpg] https://#g" > /etc/apt/sources.list.d/nvidia-container-toolkit.list &&
       apt-get update -qq && apt-get install -y -qq nvidia-container-toolkit >/dev/null; }'
+  # the node container inherits a masked /proc/driver/nvidia from the host runtime; the toolkit
+  # inside the node needs the real one to enumerate the GPUs it was given
+  cr exec "$node" umount -R /proc/driver/nvidia 2>/dev/null || true
   cr exec "$node" nvidia-ctk runtime configure --runtime=containerd --set-as-default --cdi.enabled
   cr exec "$node" systemctl restart containerd
   cr exec "$node" nvidia-smi -L

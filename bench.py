@@ -87,7 +87,8 @@ class ClockSampler:
         self._thr = None
         self.err = None
 
-    def __enter__(self):
+    def prepare(self):
+        """NVML start-up (tens of ms, takes driver locks): done BEFORE the timed region, never inside it."""
         if not self.enabled:
             self.err = "disabled (--no-clocks)"
             return self
@@ -103,10 +104,16 @@ class ClockSampler:
             self._nv = pynvml
             self._h = pynvml.nvmlDeviceGetHandleByIndex(idx)
             self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
-            self._thr = threading.Thread(target=self._run, daemon=True)
-            self._thr.start()
+            pynvml.nvmlDeviceGetClockInfo(self._h, pynvml.NVML_CLOCK_SM)  # first query pays the set-up cost
+            self._ready = True
         except Exception as e:  # NVML missing: report it, do not invent clocks
             self.err = f"{type(e).__name__}: {e}"
+        return self
+
+    def __enter__(self):
+        if getattr(self, "_ready", False):
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
         return self
 
     def _run(self):
@@ -325,9 +332,10 @@ def run_ours(args, rank, local_rank, world):
 
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
     t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler = ClockSampler(local_rank, period_s=args.clock_period_ms / 1e3, enabled=not args.no_clocks).prepare()
     barrier()
     torch.cuda.synchronize()
-    with ClockSampler(local_rank, enabled=not args.no_clocks) as clk:
+    with sampler as clk:
         t_start.record()
         for k in range(args.steps):
             step(evs[k])
@@ -344,7 +352,15 @@ def run_ours(args, rank, local_rank, world):
     my_lanes = rank_lanes if dist is None else tuple(int(x) for x in total.cpu().numpy().view(np.uint64))
 
     nccl_ms_step = None
+    per_rank = None
     if dist is not None:
+        # every rank's own view of the timed region (rank 0 prints them: shows which GPU the others wait for)
+        mine_stats = torch.tensor([ms_total / args.steps, sum(triad_ms) / len(triad_ms), sum(csum_ms) / len(csum_ms)],
+                                  dtype=torch.float64, device="cuda")
+        all_stats = [torch.empty_like(mine_stats) for _ in range(world)]
+        dist.all_gather(all_stats, mine_stats)
+        per_rank = [{"rank": r, "ms_per_step": round(float(v[0]), 4), "triad_ms": round(float(v[1]), 4),
+                     "checksum_incl_wait_ms": round(float(v[2]), 4)} for r, v in enumerate(all_stats)]
         t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total = float(t.item())
@@ -411,6 +427,7 @@ def run_ours(args, rank, local_rank, world):
         if nvlink is not None:
             line["nvlink"] = nvlink
         if dist is not None:
+            line["per_rank"] = per_rank
             line["combine"] = {"how": combine, "ms_per_step_with_nccl_combine": nccl_ms_step,
                                "launches_per_step": 2 if xchg is not None else 4}
             line["gpu_launches"] = (2 if xchg is not None else 4) * args.steps
@@ -583,6 +600,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / parity leg")
     ap.add_argument("--no-clocks", action="store_true", help="ablation only: do not sample NVML clocks while timing")
+    ap.add_argument("--clock-period-ms", type=float, default=100.0, help="NVML sampling period during the timed region")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3  # timing rule: at least 3 warm-up steps

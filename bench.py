@@ -410,6 +410,7 @@ def run_ours(args, rank, local_rank, world):
                 "traffic": (traffic or {}).get("triad_dram_bytes_per_launch"),
                 "algorithmic_bytes_per_launch": BYTES_TRIAD * n,
                 "avg_launch_ms": round(t_avg, 4), "best_launch_ms": round(min(triad_ms), 4),
+                "triad_pace_ns": gpuprobe.triad_pace_ns(),  # AUTO's per-device calibration (> 0: paced TMA kernel)
             },
             "kernels": {
                 "triad": {"bytes": BYTES_TRIAD * n, "avg_ms": round(t_avg, 4), "best_ms": round(min(triad_ms), 4),
@@ -588,7 +589,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--log2n", type=int, default=29, help="fp64 elements per array per GPU (29 = BASELINE 4 GiB)")
-    ap.add_argument("--variant", choices=["auto", "ldg128", "tma", "ldg256"], default="auto")
+    ap.add_argument("--variant", choices=["auto", "ldg128", "tma", "ldg256", "tma_paced"], default="auto")
     ap.add_argument("--e2e-log2n", type=int, default=29)
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--e2e-warmup", type=int, default=1)

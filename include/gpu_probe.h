@@ -46,6 +46,7 @@ extern "C" {
 #define GPU_PROBE_VARIANT_LDG 0     /* 128-bit coalesced ld/st, streaming hints   */
 #define GPU_PROBE_VARIANT_TMA 1     /* cp.async.bulk + mbarrier smem ring         */
 #define GPU_PROBE_VARIANT_LDG256 2  /* 256-bit ld/st (sm_100 v4.b64)              */
+#define GPU_PROBE_VARIANT_TMA_PACED 3 /* TMA ring with paced refills (triad only)   */
 
 /* Probe-level errors (<= -100). */
 #define GPU_PROBE_EINVAL (-100)    /* null pointer, bad variant, bad size         */
@@ -69,9 +70,19 @@ int gpu_probe_init_fill(double *dst, uint64_t n, uint64_t first_index,
                         uint64_t seed, void *stream);
 
 /* K1  a[k] = fma(s, c[k], b[k]), one rounding.  24 bytes of HBM traffic per
- * element.  (slot: pods/nvidia-gpu-test-pod.yaml:9; spec: SURVEY 8d "Triad") */
+ * element.  (slot: pods/nvidia-gpu-test-pod.yaml:9; spec: SURVEY 8d "Triad")
+ * VARIANT_AUTO with n >= 2^26 and 16-byte-aligned pointers uses the paced TMA kernel at a
+ * pace calibrated per device: the FIRST such call on a device [blocking] times 30 short
+ * launches on the caller's own buffers (harmless: the triad is idempotent) and synchronises
+ * the stream once, about 25 ms, once per device per process -- make it before timing or
+ * capturing (inside a stream capture AUTO silently uses the unpaced ring instead).
+ * Environment: GPU_PROBE_TRIAD_PACE_NS=0 disables the paced kernel, =N fixes the pace. */
 int gpu_probe_triad(double *a, const double *b, const double *c, double s,
                     uint64_t n, int variant, void *stream);
+
+/* What VARIANT_AUTO's calibration decided for the current device: 0 = not calibrated yet,
+ * < 0 = the unpaced ring is at least as fast here, > 0 = nanoseconds between a CTA's refills. */
+int gpu_probe_triad_pace_ns(void);
 
 /* Bytes of device scratch the checksum kernels need (a constant). */
 size_t gpu_probe_checksum_workspace_bytes(void);

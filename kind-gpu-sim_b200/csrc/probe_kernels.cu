@@ -292,6 +292,129 @@ triad_tma(double *__restrict__ a, const double *__restrict__ b, const double *__
   if (LANES) finish_lanes(acc, first, out, ws, red, x);
 }
 
+// K1 with PACED refills.  The unpaced ring above is ack-clocked: a slot is refilled the moment
+// it drains, so requests reach the memory system in bursts, and the ring has to be kept small
+// (64 KiB in flight per SM) or mixed read/write traffic over-subscribes HBM and collapses.
+// Here thread 0 spaces its refills `pace_ns` apart instead (8 KiB tiles, 4 stages, 2 CTAs/SM:
+// one 24 KiB tile set per CTA per ~1 us).  Smooth demand just under what the memory system can
+// sustain measured 7150-7190 GB/s against 6850 for the ring on the same GPU -- but 1 % beyond the
+// sustainable rate the kernel falls into the over-subscribed regime (5400-6300 GB/s), and where
+// that cliff is differs from GPU to GPU.  Hence:
+//   * the pace is given in NANOSECONDS and converted with a running estimate of the SM clock
+//     (clock64 against %globaltimer), so a power-capped clock does not change the demand rate;
+//   * the host calibrates the pace per device (calibrate_triad_pace below);
+//   * a one-way ladder guards against drift: over-subscription shows as long consumer stalls
+//     (>= 800 cycles on ~16 % of the tiles instead of 0.3 %); a CTA that sees 5 of them in 64
+//     tiles stops refilling, lets its ring drain and restarts 2 % slower.  It never speeds up.
+// tools/tune/tune_triad.cu (modes hist, ladder, ladderns) holds the experiments.
+template <int TILE, int S, bool LANES>
+__global__ void __launch_bounds__(kThreads)
+triad_tma_paced(double *__restrict__ a, const double *__restrict__ b, const double *__restrict__ c, double s, uint64_t n,
+                uint64_t first, uint64_t *__restrict__ out, uint64_t *__restrict__ ws, const ExchangeArgs x, int pace_ns) {
+  static_assert(TILE % (2 * kThreads) == 0, "tile must split into one f64x2 per thread per pass");
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  double *sb = reinterpret_cast<double *>(smem_raw);
+  double *sc = sb + size_t(S) * TILE;
+  uint64_t *full = reinterpret_cast<uint64_t *>(sc + size_t(S) * TILE);
+  __shared__ uint64_t red[64];
+  constexpr uint32_t kTileBytes = TILE * sizeof(double);
+  constexpr int kStallCycles = 800, kBadTiles = 5, kWindowTiles = 64;
+
+  const uint64_t ntiles = n / TILE;
+  const uint64_t my_tiles = ntiles > blockIdx.x ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const int tid = threadIdx.x;
+
+  uint64_t policy = 0;
+  if (tid == 0) {
+    for (int i = 0; i < S; ++i) tma::mbar_init(&full[i], 1);
+    tma::fence_barrier_init();
+    policy = tma::policy_evict_first();
+  }
+  __syncthreads();
+  // thread 0 only: producer position, pacing clock, ladder state
+  uint64_t pj = 0;
+  int pst = 0;
+  auto issue = [&]() {
+    const uint64_t t = blockIdx.x + pj * gridDim.x;
+    tma::mbar_arrive_expect_tx(&full[pst], 2 * kTileBytes);
+    tma::bulk_load(sb + size_t(pst) * TILE, b + t * TILE, kTileBytes, &full[pst], policy);
+    tma::bulk_load(sc + size_t(pst) * TILE, c + t * TILE, kTileBytes, &full[pst], policy);
+    ++pj;
+    if (++pst == S) pst = 0;
+  };
+  long long next_ok = 0, c_start = 0;
+  unsigned long long g_start = 0;
+  int pace_cur_ns = pace_ns, bad = 0, win = 0;
+  long long pace = (long long)pace_ns * 2;  // cycles; first guess 2 GHz, corrected after 64 tiles
+  bool draining = false;
+  uint64_t grace_until = 0;
+  if (tid == 0) { c_start = clock64(); g_start = global_ns(); }
+
+  Lanes acc{0, 0};
+  int st = 0;
+  uint32_t parity = 0;
+  uint64_t t = blockIdx.x;
+  for (uint64_t j = 0; j < my_tiles; ++j, t += gridDim.x) {
+    long long t0 = 0;
+    if (tid == 0) {
+      if ((j & 63) == 63) {  // refresh the cycles-per-nanosecond estimate
+        const long long dg = (long long)(global_ns() - g_start);
+        const long long dc = clock64() - c_start;
+        if (dg > 20000) pace = (long long)pace_cur_ns * dc / dg;
+      }
+      if (pj <= j) {  // ring empty: first tile of the kernel, or the drain after a fallback is complete
+        draining = false;
+        for (int i = 0; i < S && pj < my_tiles; ++i) issue();
+        next_ok = clock64() + pace;
+        grace_until = j + 2 * S + 8;  // the start-up burst is not evidence of anything
+        bad = win = 0;
+      }
+      t0 = clock64();
+    }
+    tma::mbar_wait(&full[st], parity);  // (other threads may get here before thread 0 issued: the phase cannot flip without it)
+    if (tid == 0 && !draining && j >= grace_until) {
+      if (clock64() - t0 >= kStallCycles) ++bad;
+      if (++win == kWindowTiles) {
+        if (bad >= kBadTiles) {  // over-subscribed: drain, then restart one step slower
+          draining = true;
+          const int step = pace_ns / 50;
+          pace = pace * (pace_cur_ns + step) / pace_cur_ns;
+          pace_cur_ns += step;
+        }
+        bad = win = 0;
+      }
+    }
+    const f64x2 *pb = reinterpret_cast<const f64x2 *>(sb + size_t(st) * TILE);
+    const f64x2 *pc = reinterpret_cast<const f64x2 *>(sc + size_t(st) * TILE);
+    f64x2 *ga = reinterpret_cast<f64x2 *>(a + t * TILE);
+#pragma unroll
+    for (int v = tid; v < TILE / 2; v += kThreads) {
+      const f64x2 r = fma_vec(s, pc[v], pb[v]);
+      st_stream(ga + v, r);
+      if (LANES) lanes_vec(acc, r, t * TILE + 2 * uint64_t(v));
+    }
+    __syncthreads();  // every thread is done reading slot st
+    if (tid == 0 && !draining && pj < my_tiles && pj > j + 1) {  // (pj == j+1: the ring just emptied -> restart at the loop top)
+      while (clock64() < next_ok) { }
+      next_ok += pace;
+      const long long now = clock64();
+      if (next_ok < now) next_ok = now;  // never bank credit: a late refill does not allow a burst
+      issue();
+    }
+    if (++st == S) { st = 0; parity ^= 1u; }
+  }
+
+  // remainder [ntiles*TILE, n): fewer than TILE elements, plain accesses
+  if (blockIdx.x == gridDim.x - 1) {
+    for (uint64_t k = ntiles * TILE + tid; k < n; k += kThreads) {
+      const double r = __fma_rn(s, c[k], b[k]);
+      a[k] = r;
+      if (LANES) acc.add(bits(r), 2 * k + 1);
+    }
+  }
+  if (LANES) finish_lanes(acc, first, out, ws, red, x);
+}
+
 template <int TILE, int S>
 struct ChecksumTmaSmem {
   static constexpr size_t kBytes = sizeof(uint64_t) * TILE * S + sizeof(uint64_t) * S;
@@ -530,6 +653,10 @@ static int g_auto_checksum = GPU_PROBE_VARIANT_TMA;
 //   checksum: read-only traffic has no such collapse: 32 KiB tiles, 4 stages, 1 CTA/SM
 //             = 128 KiB in flight per SM -> 7420 GB/s.
 constexpr int kTriadTile = 512, kTriadStages = 4, kTriadCtasPerSm = 2;
+// paced triad: 8 KiB tiles, 4 stages, 2 CTAs/SM (128 KiB of ring per SM; the pace, not the ring, bounds what is in flight)
+constexpr int kPacedTile = 1024, kPacedStages = 4, kPacedCtasPerSm = 2;
+constexpr int kPacedDefaultNs = 1040;          // explicit VARIANT_TMA_PACED without calibration: a conservative pace
+constexpr uint64_t kPacedMinElems = 1ull << 26;  // below 512 MiB per array the ring kernel is used: nothing to pace
 constexpr int kChecksumTile = 4096, kChecksumStages = 4, kChecksumCtasPerSm = 1;
 // LDG geometry from the same sweeps: mixed read/write traffic wants FEW resident CTAs
 // (triad: 2/SM with 8x16 B or 4x32 B loads per array per thread -> 6700 / 6530 GB/s;
@@ -538,19 +665,134 @@ constexpr int kCopyTileBytes = 32 * 1024, kCopyStages = 3;
 constexpr int kLdgTriadCtasPerSm = 2;
 constexpr int kLdgChecksumCtasPerSm = 6;
 
+// Per-device pace of the paced triad: 0 = not calibrated yet, < 0 = calibrated, the ring kernel is
+// at least as fast here, > 0 = nanoseconds between refills.  GPU_PROBE_TRIAD_PACE_NS overrides
+// (0 disables the paced kernel, N fixes the pace).
+static std::atomic<int> g_pace_ns[64];
+
+template <bool LANES>
+static int launch_triad_paced(double *a, const double *b, const double *c, double s, uint64_t n, uint64_t first,
+                              uint64_t *out, uint64_t *ws, cudaStream_t st, const ExchangeArgs &x, int pace_ns) {
+  auto k = triad_tma_paced<kPacedTile, kPacedStages, LANES>;
+  constexpr size_t smem = TriadTmaSmem<kPacedTile, kPacedStages>::kBytes;
+  unsigned grid = 1;
+  int rc = persistent_grid(k, smem, n / kPacedTile, &grid, kPacedCtasPerSm);
+  if (rc) return rc;
+  k<<<grid, kThreads, smem, st>>>(a, b, c, s, n, first, out, ws, x, pace_ns);
+  return launch_rc();
+}
+
+// First AUTO call on a device with a large aligned problem: time the ring kernel and the paced
+// kernel at a ladder of paces on the caller's own buffers (the triad is idempotent: whatever
+// these launches write into a[] the real launch writes again), keep the fastest pace that
+// behaved, one notch slower for margin.  30 launches over at most 2^28 elements, then ONE
+// stream synchronisation: about 25 ms, once per device per process.
+static int calibrate_triad_pace(double *a, const double *b, const double *c, double s, uint64_t n, cudaStream_t st,
+                                int dev) {
+  static const int paces[] = {1004, 1010, 1016, 1023, 1030, 1040, 1052, 1066, 1082};
+  constexpr int kN = int(sizeof(paces) / sizeof(paces[0]));
+  constexpr int kRuns = 2;  // timed launches per candidate, after one warm-up launch
+  const uint64_t m = n < (1ull << 28) ? n : (1ull << 28);
+  cudaEvent_t ev[2 * (kN + 1)];
+  for (auto &e : ev)
+    if (cudaEventCreate(&e) != cudaSuccess) return int(cudaGetLastError());
+  int rc = 0;
+  unsigned paced_grid = 1;
+  {
+    auto k = triad_tma_paced<kPacedTile, kPacedStages, false>;
+    rc = persistent_grid(k, TriadTmaSmem<kPacedTile, kPacedStages>::kBytes, m / kPacedTile, &paced_grid, kPacedCtasPerSm);
+  }
+  auto launch = [&](int pace_ns) {
+    if (pace_ns > 0) return launch_triad_paced<false>(a, b, c, s, m, 0, nullptr, nullptr, st, ExchangeArgs{}, pace_ns);
+    auto k = triad_tma<kTriadTile, kTriadStages, false>;
+    constexpr size_t smem = TriadTmaSmem<kTriadTile, kTriadStages>::kBytes;
+    unsigned grid = 1;
+    int r = persistent_grid(k, smem, m / kTriadTile, &grid, kTriadCtasPerSm);
+    if (r) return r;
+    k<<<grid, kThreads, smem, st>>>(a, b, c, s, m, 0, nullptr, nullptr, ExchangeArgs{});
+    return launch_rc();
+  };
+  auto timed = [&](int slot, int pace_ns) {
+    if (rc == 0) rc = launch(pace_ns);
+    cudaEventRecord(ev[2 * slot], st);
+    for (int r = 0; r < kRuns && rc == 0; ++r) rc = launch(pace_ns);
+    cudaEventRecord(ev[2 * slot + 1], st);
+  };
+  timed(kN, 0);
+  for (int i = 0; i < kN; ++i) timed(i, paces[i]);
+  if (rc == 0 && cudaStreamSynchronize(st) != cudaSuccess) rc = int(cudaGetLastError());
+  int chosen = -1;
+  if (rc == 0) {
+    float ring = 0.f, t[kN];
+    cudaEventElapsedTime(&ring, ev[2 * kN], ev[2 * kN + 1]);
+    const double tiles_per_cta = double((m / kPacedTile + paced_grid - 1) / paced_grid);
+    int best = -1;
+    for (int i = 0; i < kN; ++i) {
+      cudaEventElapsedTime(&t[i], ev[2 * i], ev[2 * i + 1]);
+      // "behaved": pace-limited -- the launches took what the pace allows (+3 %); a collapsed run is 15-30 % off
+      const double ideal_ms = kRuns * tiles_per_cta * paces[i] * 1e-6;
+      if (t[i] <= ideal_ms * 1.03 && (best < 0 || t[i] < t[best])) best = i;
+    }
+    if (best >= 0) {
+      const int safe = best + 1 < kN ? best + 1 : best;  // one notch (~0.7 %) slower than the fastest that behaved
+      if (t[safe] < ring * 0.995f) chosen = paces[safe];
+    }
+  }
+  for (auto &e : ev) cudaEventDestroy(e);
+  if (rc) return rc;
+  g_pace_ns[dev].store(chosen, std::memory_order_release);
+  return 0;
+}
+
+// Pace for an AUTO call on the current device (calibrating if this is the first one), or <= 0 for "use the ring".
+static int auto_triad_pace(double *a, const double *b, const double *c, double s, uint64_t n, cudaStream_t st, int *pace) {
+  static const int forced = [] { const char *e = getenv("GPU_PROBE_TRIAD_PACE_NS"); return e ? atoi(e) : -1; }();
+  *pace = -1;
+  if (forced >= 0) { *pace = forced; return 0; }
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return int(e);
+  if (dev < 0 || dev >= 64) return 0;
+  int p = g_pace_ns[dev].load(std::memory_order_acquire);
+  if (p == 0) {
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(st, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) {
+      cudaGetLastError();
+      return 0;  // never calibrate (and synchronise) inside a capture: ring kernel, calibrate another time
+    }
+    int rc = calibrate_triad_pace(a, b, c, s, n, st, dev);
+    if (rc) return rc;
+    p = g_pace_ns[dev].load(std::memory_order_acquire);
+  }
+  *pace = p;
+  return 0;
+}
+
 template <bool LANES>
 static int launch_triad(double *a, const double *b, const double *c, double s, uint64_t n, uint64_t first,
                         uint64_t *out, uint64_t *ws, int variant, cudaStream_t st, const ExchangeArgs &x) {
-  if (variant == GPU_PROBE_VARIANT_AUTO) variant = g_auto_triad;
   const bool al16 = aligned(a, 16) && aligned(b, 16) && aligned(c, 16);
   const bool al32 = aligned(a, 32) && aligned(b, 32) && aligned(c, 32);
   unsigned grid = 1;
   int rc;
+  if (variant == GPU_PROBE_VARIANT_AUTO) {
+    variant = g_auto_triad;
+    if (al16 && n >= kPacedMinElems) {
+      int pace = -1;
+      if ((rc = auto_triad_pace(a, b, c, s, n, st, &pace))) return rc;
+      if (pace > 0) return launch_triad_paced<LANES>(a, b, c, s, n, first, out, ws, st, x, pace);
+    }
+  }
   if (!al16) {
     auto k = triad_scalar<LANES>;
     if ((rc = persistent_grid(k, 0, (n + kThreads - 1) / kThreads, &grid))) return rc;
     k<<<grid, kThreads, 0, st>>>(a, b, c, s, n, first, out, ws, x);
     return launch_rc();
+  }
+  if (variant == GPU_PROBE_VARIANT_TMA_PACED) {
+    int dev = 0, pace = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < 64) pace = g_pace_ns[dev].load(std::memory_order_acquire);
+    return launch_triad_paced<LANES>(a, b, c, s, n, first, out, ws, st, x, pace > 0 ? pace : kPacedDefaultNs);
   }
   if (variant == GPU_PROBE_VARIANT_TMA) {
     auto k = triad_tma<kTriadTile, kTriadStages, LANES>;
@@ -580,7 +822,7 @@ static int launch_triad(double *a, const double *b, const double *c, double s, u
 }
 
 static int check_variant(int v) {
-  return (v >= GPU_PROBE_VARIANT_AUTO && v <= GPU_PROBE_VARIANT_LDG256) ? 0 : GPU_PROBE_EINVAL;
+  return (v >= GPU_PROBE_VARIANT_AUTO && v <= GPU_PROBE_VARIANT_TMA_PACED) ? 0 : GPU_PROBE_EINVAL;
 }
 
 // Argument checks + launch of K2; `x.world > 0` attaches the lanes exchange (probe_exchange.cu).
@@ -591,7 +833,7 @@ int checked_checksum(const uint64_t *w, uint64_t n, uint64_t first_index, uint64
   if (!aligned(w, 8) || !aligned(out_lanes, 8) || !aligned(workspace, 8)) return GPU_PROBE_EALIGN;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   uint64_t *ws = static_cast<uint64_t *>(workspace);
-  if (variant == GPU_PROBE_VARIANT_AUTO) variant = g_auto_checksum;
+  if (variant == GPU_PROBE_VARIANT_AUTO || variant == GPU_PROBE_VARIANT_TMA_PACED) variant = g_auto_checksum;  // read-only traffic has nothing to pace
   unsigned grid = 1;
   int rc;
   if (!aligned(w, 16)) {
@@ -663,7 +905,7 @@ int gpu_probe_abi_version(void) { return GPU_PROBE_ABI_VERSION; }
 
 const char *gpu_probe_kernel_info(void) {
   return "gpu-probe abi=1 arch=sm_100a kernels=init_fill,triad,checksum_u64,triad_checksum,p2p_copy,lanes_exchange "
-         "variants=ldg128,tma_bulk,ldg256 cpu_fallback=none";
+         "variants=ldg128,tma_bulk,ldg256,tma_paced cpu_fallback=none";
 }
 
 const char *gpu_probe_error_string(int rc) {
@@ -707,6 +949,12 @@ int gpu_probe_triad(double *a, const double *b, const double *c, double s, uint6
   if (!aligned(a, 8) || !aligned(b, 8) || !aligned(c, 8)) return GPU_PROBE_EALIGN;
   return launch_triad<false>(a, b, c, s, n, 0, nullptr, nullptr, variant, static_cast<cudaStream_t>(stream),
                              ExchangeArgs{});
+}
+
+int gpu_probe_triad_pace_ns(void) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
+  return g_pace_ns[dev].load(std::memory_order_acquire);
 }
 
 size_t gpu_probe_checksum_workspace_bytes(void) { return kWorkspaceBytes; }

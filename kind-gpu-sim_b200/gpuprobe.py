@@ -19,8 +19,9 @@ SEED_B = 0x0123456789ABCDEF
 SEED_C = 0xFEDCBA9876543210
 SCALAR = 3.0
 
-VARIANT_AUTO, VARIANT_LDG, VARIANT_TMA, VARIANT_LDG256 = -1, 0, 1, 2
-VARIANTS = {"auto": VARIANT_AUTO, "ldg128": VARIANT_LDG, "tma": VARIANT_TMA, "ldg256": VARIANT_LDG256}
+VARIANT_AUTO, VARIANT_LDG, VARIANT_TMA, VARIANT_LDG256, VARIANT_TMA_PACED = -1, 0, 1, 2, 3
+VARIANTS = {"auto": VARIANT_AUTO, "ldg128": VARIANT_LDG, "tma": VARIANT_TMA, "ldg256": VARIANT_LDG256,
+            "tma_paced": VARIANT_TMA_PACED}
 
 EINVAL, EALIGN, ETOOBIG, ENOTREADY, ETIMEDOUT = -100, -101, -102, -103, -104
 EXCHANGE_MAX_RANKS, EXCHANGE_HANDLE_BYTES = 16, 64
@@ -108,6 +109,13 @@ def error_string(rc: int) -> str:
 
 def kernel_info() -> str:
     return lib().gpu_probe_kernel_info().decode()
+
+
+def triad_pace_ns() -> int:
+    """AUTO's calibrated pace on the current device (0: not yet, < 0: unpaced ring, > 0: ns per refill)."""
+    L = lib()
+    L.gpu_probe_triad_pace_ns.restype = ctypes.c_int
+    return int(L.gpu_probe_triad_pace_ns())
 
 
 def workspace_bytes() -> int:

@@ -359,9 +359,9 @@ static int phase_hbm(const options *o, gpu_state *gs, int ng, uint64_t n) {
       int known = 0;
       if ((k == K_CHECKSUM || k == K_FUSED) && ng == 1) match = match_known(n, gs[d].h_lanes + (k == K_FUSED ? 2 : 0), &known);
       printf("RESULT kind=%s gpus=%d gpu=%d bytes=%" PRIu64 " ms=%.4f ms_med=%.4f gbs=%.1f frac_nominal=%.4f "
-             "frac_measured=%s lanes=%s match=%s variant=%s\n",
+             "frac_measured=%s lanes=%s match=%s variant=%s pace_ns=%d\n",
              k_name[k], ng, gs[d].dev, bytes, t.best_ms, t.med_ms, gbs, gbs / NOMINAL_HBM_GBS, fm, lanes, match,
-             o->variant_name);
+             o->variant_name, (k == K_TRIAD || k == K_FUSED) ? gpu_probe_triad_pace_ns() : 0);
       sum_gbs += (double)bytes / (t.med_ms * 1e-3) / 1e9;
       if (t.med_ms > worst_ms) worst_ms = t.med_ms;
     }

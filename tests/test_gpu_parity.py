@@ -16,8 +16,9 @@ from gpu_util import (M64, f64, from_np, gpu_checksum, gpu_init, hx, lanes_buf, 
 
 pytestmark = pytest.mark.gpu
 
-VARIANTS = [gpuprobe.VARIANT_LDG, gpuprobe.VARIANT_TMA, gpuprobe.VARIANT_LDG256, gpuprobe.VARIANT_AUTO]
-VNAMES = ["ldg128", "tma", "ldg256", "auto"]
+VARIANTS = [gpuprobe.VARIANT_LDG, gpuprobe.VARIANT_TMA, gpuprobe.VARIANT_LDG256, gpuprobe.VARIANT_TMA_PACED,
+            gpuprobe.VARIANT_AUTO]
+VNAMES = ["ldg128", "tma", "ldg256", "tma_paced", "auto"]
 # ragged sizes around every tiling boundary: vector width, CTA tile (256*U), TMA tiles (1024 / 4096)
 SIZES = [0, 1, 2, 3, 4, 5, 255, 256, 257, 1023, 1024, 1025, 2047, 2048, 2049, 4095, 4096, 4096 + 3, 8192 + 1, 65536,
          (1 << 20) + 3, 148 * 4096 * 3 + 4095,
@@ -246,7 +247,8 @@ def test_beyond_2_32_elements_matches_golden(golden):
                             ws.data_ptr(), gpuprobe.VARIANT_TMA, stream())
     torch.cuda.synchronize()
     assert lanes_of(out) == want, hx(lanes_of(out))
-    for variant in (gpuprobe.VARIANT_LDG, gpuprobe.VARIANT_LDG256, gpuprobe.VARIANT_TMA):
+    for variant in (gpuprobe.VARIANT_LDG, gpuprobe.VARIANT_LDG256, gpuprobe.VARIANT_TMA, gpuprobe.VARIANT_TMA_PACED,
+                    gpuprobe.VARIANT_AUTO):
         a.zero_()
         gpuprobe.triad(a.data_ptr(), b.data_ptr(), c.data_ptr(), gpuprobe.SCALAR, n, variant, stream())
         assert gpu_checksum(a, 0, variant, ws) == want, variant
@@ -257,3 +259,21 @@ def test_beyond_2_32_elements_matches_golden(golden):
     assert got == ((want[0] - lower[0]) & M64, (want[1] - lower[1]) & M64)
     del a, b, c
     torch.cuda.empty_cache()
+
+
+def test_auto_triad_calibrates_once_and_stays_bit_exact(golden):
+    """AUTO at >= 2^26 elements calibrates a per-device pace on first use (timed launches on the
+    caller's buffers) and then runs the paced kernel: whatever pace it picks, the bits are the same."""
+    n = 1 << 27
+    want = tuple(int(v, 16) for v in golden["pow2_lanes"][27])
+    b, c, a = gpu_init(n, 0, oracle.SEED_B), gpu_init(n, 0, oracle.SEED_C), f64(n)
+    ws = workspace()
+    for rep in range(3):
+        a.fill_(-1.0)
+        gpuprobe.triad(a.data_ptr(), b.data_ptr(), c.data_ptr(), gpuprobe.SCALAR, n, gpuprobe.VARIANT_AUTO, stream())
+        assert gpu_checksum(a, 0, gpuprobe.VARIANT_AUTO, ws) == want, rep
+    out = lanes_buf()
+    gpuprobe.triad_checksum(a.data_ptr(), b.data_ptr(), c.data_ptr(), gpuprobe.SCALAR, n, 0, out.data_ptr(), ws.data_ptr(),
+                            gpuprobe.VARIANT_TMA_PACED, stream())
+    torch.cuda.synchronize()
+    assert lanes_of(out) == want

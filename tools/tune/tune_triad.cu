@@ -336,7 +336,7 @@ __global__ void checksum_tma_rt(const uint64_t *__restrict__ w, uint64_t n, uint
     __syncthreads();
     if (tid == 0 && j + S < my_tiles) issue(j + S);
   }
-  finish_lanes(acc, 0, out, ws, red);
+  finish_lanes(acc, 0, out, ws, red, ExchangeArgs{});
 }
 template <typename V, int U>
 __global__ void checksum_ldg_rt(const V *__restrict__ w, uint64_t nvec, uint64_t *__restrict__ out, uint64_t *__restrict__ ws) {
@@ -355,7 +355,7 @@ __global__ void checksum_ldg_rt(const V *__restrict__ w, uint64_t nvec, uint64_t
       else acc4(acc, *reinterpret_cast<u64x4 *>(&v[u]), (i0 + uint64_t(u) * blockDim.x) * E);
     }
   }
-  finish_lanes(acc, 0, out, ws, red);
+  finish_lanes(acc, 0, out, ws, red, ExchangeArgs{});
 }
 
 struct Timer {
@@ -378,6 +378,369 @@ struct Timer {
     *med = ms[iters / 2];
   }
 };
+
+
+// Adaptive pacing ("congestion control" for HBM): thread 0 spaces its refills `pace` cycles apart
+// and adapts the pace from what the consumers see.  If the data of the next tile is not there
+// when the CTA needs it (stall at the mbarrier), demand exceeds what the memory system delivers
+// -> slow down (additive increase of the pace); after `calm_n` tiles without a stall -> speed up.
+// Fixed pacing reached 7110 GB/s at exactly the right pace and collapsed 2.5 % beyond it, and
+// the right pace differs per GPU; the controller is meant to find it on its own.
+__global__ void __launch_bounds__(256)
+triad_tma_adapt(double *__restrict__ a, const double *__restrict__ b, const double *__restrict__ c, double s,
+                uint64_t n, int tile, int S, int pace0, int inc, int dec, int thresh, int calm_n, int pace_min,
+                int *__restrict__ pace_out) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  double *sb = reinterpret_cast<double *>(smem_raw);
+  double *sc = sb + size_t(S) * tile;
+  uint64_t *full = reinterpret_cast<uint64_t *>(sc + size_t(S) * tile);
+  const uint32_t tile_bytes = uint32_t(tile) * 8u;
+  const uint64_t ntiles = n / tile;
+  const uint64_t my_tiles = ntiles > blockIdx.x ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const int tid = threadIdx.x;
+  uint64_t policy = 0;
+  if (tid == 0) {
+    for (int i = 0; i < S; ++i) tma::mbar_init(&full[i], 1);
+    tma::fence_barrier_init();
+  }
+  __syncthreads();
+  uint64_t pj = 0;
+  int pst = 0;
+  long long next_ok = 0;
+  int pace = pace0, calm = 0;
+  long long pace_sum = 0;
+  auto issue = [&]() {
+    const uint64_t t = blockIdx.x + pj * gridDim.x;
+    tma::mbar_arrive_expect_tx(&full[pst], 2 * tile_bytes);
+    tma::bulk_load(sb + size_t(pst) * tile, b + t * tile, tile_bytes, &full[pst], policy);
+    tma::bulk_load(sc + size_t(pst) * tile, c + t * tile, tile_bytes, &full[pst], policy);
+    ++pj;
+    if (++pst == S) pst = 0;
+  };
+  if (tid == 0) {
+    policy = tma::policy_evict_first();
+    for (int i = 0; i < S && pj < my_tiles; ++i) issue();
+    next_ok = clock64() + pace;
+  }
+  int st = 0;
+  uint32_t parity = 0;
+  uint64_t t = blockIdx.x;
+  for (uint64_t j = 0; j < my_tiles; ++j, t += gridDim.x) {
+    long long t0 = 0;
+    if (tid == 0) t0 = clock64();
+    tma::mbar_wait(&full[st], parity);
+    if (tid == 0) {
+      const long long stall = clock64() - t0;
+      if (pace_out) {
+        const int bkt = stall < 100 ? 0 : stall < 200 ? 1 : stall < 400 ? 2 : stall < 800 ? 3 : stall < 1600 ? 4 : stall < 3200 ? 5 : 6;
+        atomicAdd(&pace_out[8192 + bkt], 1);
+      }
+      if (stall > thresh) { pace += inc; calm = 0; }
+      else if (++calm >= calm_n) { pace -= dec; calm = 0; if (pace < pace_min) pace = pace_min; }
+      pace_sum += pace;
+    }
+    const f64x2 *pb = reinterpret_cast<const f64x2 *>(sb + size_t(st) * tile);
+    const f64x2 *pc = reinterpret_cast<const f64x2 *>(sc + size_t(st) * tile);
+    f64x2 *ga = reinterpret_cast<f64x2 *>(a + t * tile);
+#pragma unroll 4
+    for (int v = tid; v < tile / 2; v += 256) {
+      const f64x2 x = pb[v], y = pc[v];
+      st_stream(ga + v, f64x2{__fma_rn(s, y.x, x.x), __fma_rn(s, y.y, x.y)});
+    }
+    __syncthreads();
+    if (tid == 0 && pj < my_tiles) {
+      while (clock64() < next_ok) { }
+      next_ok += pace;
+      const long long now = clock64();
+      if (next_ok < now) next_ok = now;  // never bank credit
+      issue();
+    }
+    if (++st == S) { st = 0; parity ^= 1u; }
+  }
+  if (tid == 0 && pace_out) { pace_out[2 * blockIdx.x] = pace; pace_out[2 * blockIdx.x + 1] = my_tiles ? int(pace_sum / (long long)my_tiles) : 0; }
+}
+
+
+// Self-clocked pacing: refills are spaced by the CTA's own measured tile service time (EWMA of
+// the intervals between tile completions), nudged so that the number of outstanding tiles
+// stays at `target` (< S).  Demand can never run ahead of delivery for long (no fixed rate to
+// overshoot), the ring bounds the damage, and arrivals at the memory system are smooth instead
+// of ack-clocked bursts.
+__global__ void __launch_bounds__(256)
+triad_tma_selfclock(double *__restrict__ a, const double *__restrict__ b, const double *__restrict__ c, double s,
+                    uint64_t n, int tile, int S, int target, int up1024, int down1024, int ewma_shift,
+                    int *__restrict__ dbg) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  double *sb = reinterpret_cast<double *>(smem_raw);
+  double *sc = sb + size_t(S) * tile;
+  uint64_t *full = reinterpret_cast<uint64_t *>(sc + size_t(S) * tile);
+  const uint32_t tile_bytes = uint32_t(tile) * 8u;
+  const uint64_t ntiles = n / tile;
+  const uint64_t my_tiles = ntiles > blockIdx.x ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const int tid = threadIdx.x;
+  uint64_t policy = 0;
+  if (tid == 0) {
+    for (int i = 0; i < S; ++i) tma::mbar_init(&full[i], 1);
+    tma::fence_barrier_init();
+  }
+  __syncthreads();
+  uint64_t pj = 0;
+  int pst = 0;
+  auto issue = [&]() {
+    const uint64_t t = blockIdx.x + pj * gridDim.x;
+    tma::mbar_arrive_expect_tx(&full[pst], 2 * tile_bytes);
+    tma::bulk_load(sb + size_t(pst) * tile, b + t * tile, tile_bytes, &full[pst], policy);
+    tma::bulk_load(sc + size_t(pst) * tile, c + t * tile, tile_bytes, &full[pst], policy);
+    ++pj;
+    if (++pst == S) pst = 0;
+  };
+  long long last_done = 0, last_issue = 0, T = 0, out_sum = 0;
+  if (tid == 0) {
+    policy = tma::policy_evict_first();
+    for (int i = 0; i < target && pj < my_tiles; ++i) issue();
+    last_issue = clock64();
+  }
+  int st = 0;
+  uint32_t parity = 0;
+  uint64_t t = blockIdx.x;
+  for (uint64_t j = 0; j < my_tiles; ++j, t += gridDim.x) {
+    tma::mbar_wait(&full[st], parity);
+    if (tid == 0) {
+      const long long now = clock64();
+      if (last_done) {
+        const long long dt = now - last_done;
+        T = T ? T + ((dt - T) >> ewma_shift) : dt;
+      }
+      last_done = now;
+    }
+    const f64x2 *pb = reinterpret_cast<const f64x2 *>(sb + size_t(st) * tile);
+    const f64x2 *pc = reinterpret_cast<const f64x2 *>(sc + size_t(st) * tile);
+    f64x2 *ga = reinterpret_cast<f64x2 *>(a + t * tile);
+#pragma unroll 4
+    for (int v = tid; v < tile / 2; v += 256) {
+      const f64x2 x = pb[v], y = pc[v];
+      st_stream(ga + v, f64x2{__fma_rn(s, y.x, x.x), __fma_rn(s, y.y, x.y)});
+    }
+    __syncthreads();  // slot st is free again
+    if (tid == 0) {
+      // outstanding = issued - consumed (tile j is consumed now)
+      int outstanding = int(pj - (j + 1));
+      out_sum += outstanding;
+      // issue as many as the schedule allows, at most up to S-1 outstanding (one slot is being refilled next round)
+      while (pj < my_tiles && outstanding < S - 1) {
+        const long long gap = T ? (T * (outstanding >= target ? up1024 : down1024)) >> 10 : 0;
+        const long long due = last_issue + gap;
+        const long long now = clock64();
+        if (now < due) {
+          if (outstanding >= 1) break;            // data is on its way: do not sit here, come back after the next tile
+          while (clock64() < due) { }              // nothing outstanding: wait out the gap rather than starve
+        }
+        issue();
+        last_issue = clock64();
+        ++outstanding;
+      }
+    }
+    if (++st == S) { st = 0; parity ^= 1u; }
+  }
+  if (tid == 0 && dbg) { dbg[2 * blockIdx.x] = int(T); dbg[2 * blockIdx.x + 1] = my_tiles ? int(out_sum * 100 / (long long)my_tiles) : 0; }
+}
+
+
+// Optimistic pacing with a one-way ladder.  Refills are spaced `pace` cycles apart (smooth,
+// slightly below what the memory system can sustain: 7100+ GB/s).  If the memory system cannot
+// sustain it the kernel falls into the over-subscribed regime, which shows up as long consumer
+// stalls (>= 800 cycles on ~16 % of the tiles instead of 0.3 %).  Then the CTA stops refilling,
+// lets its ring drain, and restarts 2 % slower.  One-way: the pace never speeds up again.
+__global__ void __launch_bounds__(256)
+triad_tma_ladder(double *__restrict__ a, const double *__restrict__ b, const double *__restrict__ c, double s,
+                 uint64_t n, int tile, int S, int pace0, int step1024, int stall_t, int bad_n, int win_n,
+                 int *__restrict__ dbg) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  double *sb = reinterpret_cast<double *>(smem_raw);
+  double *sc = sb + size_t(S) * tile;
+  uint64_t *full = reinterpret_cast<uint64_t *>(sc + size_t(S) * tile);
+  const uint32_t tile_bytes = uint32_t(tile) * 8u;
+  const uint64_t ntiles = n / tile;
+  const uint64_t my_tiles = ntiles > blockIdx.x ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const int tid = threadIdx.x;
+  uint64_t policy = 0;
+  if (tid == 0) {
+    for (int i = 0; i < S; ++i) tma::mbar_init(&full[i], 1);
+    tma::fence_barrier_init();
+    policy = tma::policy_evict_first();
+  }
+  __syncthreads();
+  uint64_t pj = 0;
+  int pst = 0;
+  auto issue = [&]() {
+    const uint64_t t = blockIdx.x + pj * gridDim.x;
+    tma::mbar_arrive_expect_tx(&full[pst], 2 * tile_bytes);
+    tma::bulk_load(sb + size_t(pst) * tile, b + t * tile, tile_bytes, &full[pst], policy);
+    tma::bulk_load(sc + size_t(pst) * tile, c + t * tile, tile_bytes, &full[pst], policy);
+    ++pj;
+    if (++pst == S) pst = 0;
+  };
+  long long next_ok = 0;
+  int pace = pace0, bad = 0, win = 0, level = 0;
+  bool draining = false;
+  uint64_t grace_until = 0;
+  int st = 0;
+  uint32_t parity = 0;
+  uint64_t t = blockIdx.x;
+  for (uint64_t j = 0; j < my_tiles; ++j, t += gridDim.x) {
+    long long t0 = 0;
+    if (tid == 0) {
+      if (pj <= j) {  // ring empty: first tile of the kernel, or the drain after a fallback is complete
+        draining = false;
+        for (int i = 0; i < S && pj < my_tiles; ++i) issue();
+        next_ok = clock64() + pace;
+        grace_until = j + 2 * S + 8;  // the start-up burst is not evidence of anything
+        bad = win = 0;
+      }
+      t0 = clock64();
+    }
+    tma::mbar_wait(&full[st], parity);
+    if (tid == 0 && !draining && j >= grace_until) {
+      const long long stall = clock64() - t0;
+      if (stall >= stall_t) ++bad;
+      if (++win == win_n) {
+        if (bad >= bad_n) {  // over-subscribed: drain, then restart one step slower
+          draining = true;
+          pace += (pace0 * step1024) >> 10;
+          ++level;
+        }
+        bad = win = 0;
+      }
+    }
+    const f64x2 *pb = reinterpret_cast<const f64x2 *>(sb + size_t(st) * tile);
+    const f64x2 *pc = reinterpret_cast<const f64x2 *>(sc + size_t(st) * tile);
+    f64x2 *ga = reinterpret_cast<f64x2 *>(a + t * tile);
+#pragma unroll 4
+    for (int v = tid; v < tile / 2; v += 256) {
+      const f64x2 x = pb[v], y = pc[v];
+      st_stream(ga + v, f64x2{__fma_rn(s, y.x, x.x), __fma_rn(s, y.y, x.y)});
+    }
+    __syncthreads();
+    if (tid == 0 && !draining && pj < my_tiles && pj > j + 1) {  // (pj == j+1: ring just emptied, restart at the loop top)
+      while (clock64() < next_ok) { }
+      next_ok += pace;
+      const long long now = clock64();
+      if (next_ok < now) next_ok = now;  // never bank credit
+      issue();
+    }
+    if (++st == S) { st = 0; parity ^= 1u; }
+  }
+  if (tid == 0 && dbg) { dbg[2 * blockIdx.x] = pace; dbg[2 * blockIdx.x + 1] = level; }
+}
+
+
+__global__ void globaltimer_probe(unsigned long long *out) {
+  unsigned long long prev = 0, t;
+  int k = 0;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(prev));
+  const long long c0 = clock64();
+  while (k < 64) {
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    if (t != prev) { out[k++] = t - prev; prev = t; }
+  }
+  out[64] = (unsigned long long)(clock64() - c0);
+}
+
+// Ladder kernel with the pace given in NANOSECONDS: thread 0 keeps a running estimate of the SM
+// clock (clock64 against %globaltimer since kernel start) and converts, so that a power-capped
+// clock does not silently lower the demand rate.
+__global__ void __launch_bounds__(256)
+triad_tma_ladder_ns(double *__restrict__ a, const double *__restrict__ b, const double *__restrict__ c, double s,
+                    uint64_t n, int tile, int S, int pace_ns, int step1024, int stall_t, int bad_n, int win_n,
+                    int *__restrict__ dbg) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  double *sb = reinterpret_cast<double *>(smem_raw);
+  double *sc = sb + size_t(S) * tile;
+  uint64_t *full = reinterpret_cast<uint64_t *>(sc + size_t(S) * tile);
+  const uint32_t tile_bytes = uint32_t(tile) * 8u;
+  const uint64_t ntiles = n / tile;
+  const uint64_t my_tiles = ntiles > blockIdx.x ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const int tid = threadIdx.x;
+  uint64_t policy = 0;
+  if (tid == 0) {
+    for (int i = 0; i < S; ++i) tma::mbar_init(&full[i], 1);
+    tma::fence_barrier_init();
+    policy = tma::policy_evict_first();
+  }
+  __syncthreads();
+  uint64_t pj = 0;
+  int pst = 0;
+  auto issue = [&]() {
+    const uint64_t t = blockIdx.x + pj * gridDim.x;
+    tma::mbar_arrive_expect_tx(&full[pst], 2 * tile_bytes);
+    tma::bulk_load(sb + size_t(pst) * tile, b + t * tile, tile_bytes, &full[pst], policy);
+    tma::bulk_load(sc + size_t(pst) * tile, c + t * tile, tile_bytes, &full[pst], policy);
+    ++pj;
+    if (++pst == S) pst = 0;
+  };
+  long long next_ok = 0, c_start = 0;
+  unsigned long long g_start = 0;
+  int pace_cur_ns = pace_ns, bad = 0, win = 0, level = 0;
+  long long pace = (long long)pace_ns * 1965 / 1000;  // first guess: 1.965 GHz
+  bool draining = false;
+  uint64_t grace_until = 0;
+  if (tid == 0) { c_start = clock64(); asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g_start)); }
+  int st = 0;
+  uint32_t parity = 0;
+  uint64_t t = blockIdx.x;
+  for (uint64_t j = 0; j < my_tiles; ++j, t += gridDim.x) {
+    long long t0 = 0;
+    if (tid == 0) {
+      if ((j & 63) == 63) {  // refresh the cycles-per-ns estimate
+        unsigned long long g;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g));
+        const long long dc = clock64() - c_start;
+        const long long dg = (long long)(g - g_start);
+        if (dg > 20000) pace = (long long)pace_cur_ns * dc / dg;
+      }
+      if (pj <= j) {
+        draining = false;
+        for (int i = 0; i < S && pj < my_tiles; ++i) issue();
+        next_ok = clock64() + pace;
+        grace_until = j + 2 * S + 8;
+        bad = win = 0;
+      }
+      t0 = clock64();
+    }
+    tma::mbar_wait(&full[st], parity);
+    if (tid == 0 && !draining && j >= grace_until) {
+      const long long stall = clock64() - t0;
+      if (stall >= stall_t) ++bad;
+      if (++win == win_n) {
+        if (bad >= bad_n) {
+          draining = true;
+          pace_cur_ns += (pace_ns * step1024) >> 10;
+          pace = pace * pace_cur_ns / (pace_cur_ns - ((pace_ns * step1024) >> 10));
+          ++level;
+        }
+        bad = win = 0;
+      }
+    }
+    const f64x2 *pb = reinterpret_cast<const f64x2 *>(sb + size_t(st) * tile);
+    const f64x2 *pc = reinterpret_cast<const f64x2 *>(sc + size_t(st) * tile);
+    f64x2 *ga = reinterpret_cast<f64x2 *>(a + t * tile);
+#pragma unroll 4
+    for (int v = tid; v < tile / 2; v += 256) {
+      const f64x2 x = pb[v], y = pc[v];
+      st_stream(ga + v, f64x2{__fma_rn(s, y.x, x.x), __fma_rn(s, y.y, x.y)});
+    }
+    __syncthreads();
+    if (tid == 0 && !draining && pj < my_tiles && pj > j + 1) {
+      while (clock64() < next_ok) { }
+      next_ok += pace;
+      const long long now = clock64();
+      if (next_ok < now) next_ok = now;
+      issue();
+    }
+    if (++st == S) { st = 0; parity ^= 1u; }
+  }
+  if (tid == 0 && dbg) { dbg[2 * blockIdx.x] = int(pace); dbg[2 * blockIdx.x + 1] = level; }
+}
 
 int main(int argc, char **argv) {
   const int log2n = argc > 1 ? atoi(argv[1]) : 29;
@@ -645,6 +1008,200 @@ int main(int argc, char **argv) {
       for (int pace : {700, 800, 850, 900, 925, 950, 975, 1000, 1025, 1050, 1100, 1200}) run_fast(1024, S, 1, pace);
     for (int pace : {350, 400, 425, 450, 475, 500, 525, 550, 600}) run_fast(512, 8, 1, pace);
     for (int pace : {1400, 1600, 1700, 1800, 1900, 2000, 2100, 2200, 2400}) run_fast(1024, 4, 2, pace);
+  }
+
+  if (!strcmp(only, "adapt")) {
+    double *sa, *sb2, *sc2;
+    int *pace_d;
+    CK(cudaMalloc(&sb2, n * 8)); CK(cudaMalloc(&sc2, n * 8)); CK(cudaMalloc(&sa, n * 8));
+    CK(cudaMalloc(&pace_d, sizeof(int) * (2 * 4096 + 16)));
+    CK(cudaMemset(sb2, 0, n * 8)); CK(cudaMemset(sc2, 0, n * 8));
+    a = sa; b = sb2; c = sc2;
+    auto ka = triad_tma_adapt;
+    auto run_adapt = [&](int tile, int S, int ctas, int pace0, int inc, int dec, int thresh, int calm_n) {
+      const size_t smem = size_t(tile) * 8 * 2 * S + 8 * S;
+      CK(cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+      int occ = 0;
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ka, 256, smem));
+      if (occ < ctas) return;
+      const int grid = sms * ctas;
+      CK(cudaMemset(pace_d + 8192, 0, sizeof(int) * 16));
+      tm.run([&] { ka<<<grid, 256, smem>>>(a, b, c, 3.0, n, tile, S, pace0, inc, dec, thresh, calm_n, pace0 / 2, pace_d); }, 2, 10, &best, &med);
+      CK(cudaGetLastError());
+      std::vector<int> ph(2 * grid);
+      CK(cudaMemcpy(ph.data(), pace_d, sizeof(int) * 2 * grid, cudaMemcpyDeviceToHost));
+      int hist[8];
+      CK(cudaMemcpy(hist, pace_d + 8192, sizeof(hist), cudaMemcpyDeviceToHost));
+      double ht = 0;
+      for (int i = 0; i < 7; ++i) ht += hist[i];
+      fprintf(stderr, "stall_hist pace0=%d thresh=%d: <100 %.3f <200 %.3f <400 %.3f <800 %.3f <1600 %.3f <3200 %.3f >=3200 %.3f\n", pace0, thresh,
+              hist[0] / ht, hist[1] / ht, hist[2] / ht, hist[3] / ht, hist[4] / ht, hist[5] / ht, hist[6] / ht);
+      double fin = 0, avg = 0;
+      for (int i = 0; i < grid; ++i) { fin += ph[2 * i]; avg += ph[2 * i + 1]; }
+      snprintf(param, sizeof param, "tileKB=%.1f S=%d ctas=%d pace0=%d inc=%d dec=%d thresh=%d calm=%d final_pace=%.0f mean_pace=%.0f",
+               tile * 8 / 1024.0, S, ctas, pace0, inc, dec, thresh, calm_n, fin / grid, avg / grid);
+      report("triad_adapt", param, 24.0 * n, best, med);
+    };
+    // reference points: shipped kernel, fixed pacing at a few rates
+    for (int rep = 0; rep < 2; ++rep) {
+      tm.run([&] { int rc = gpu_probe_triad(a, b, c, 3.0, n, 1, nullptr); if (rc) exit(1); }, 2, 10, &best, &med);
+      report("triad_tma", "shipped", 24.0 * n, best, med);
+    }
+    for (int pace : {1900, 1950, 2000, 2050, 2100, 2200}) run_adapt(1024, 4, 2, pace, 0, 0, 1 << 30, 1 << 30);
+    for (int thresh : {50, 200, 600})
+      for (int inc : {4, 16})
+        for (int dec : {1, 4})
+          for (int calm : {4, 16})
+            run_adapt(1024, 4, 2, 2300, inc, dec, thresh, calm);
+    for (int thresh : {50, 200, 600})
+      for (int inc : {4, 16}) run_adapt(1024, 8, 1, 1150, inc, 1, thresh, 8);
+  }
+
+  if (!strcmp(only, "selfclock")) {
+    double *sa, *sb2, *sc2;
+    int *dbg_d;
+    CK(cudaMalloc(&sb2, n * 8)); CK(cudaMalloc(&sc2, n * 8)); CK(cudaMalloc(&sa, n * 8));
+    CK(cudaMalloc(&dbg_d, sizeof(int) * 2 * 4096));
+    CK(cudaMemset(sb2, 0, n * 8)); CK(cudaMemset(sc2, 0, n * 8));
+    a = sa; b = sb2; c = sc2;
+    auto ks = triad_tma_selfclock;
+    for (int rep = 0; rep < 2; ++rep) {
+      tm.run([&] { int rc = gpu_probe_triad(a, b, c, 3.0, n, 1, nullptr); if (rc) exit(1); }, 2, 10, &best, &med);
+      report("triad_tma", "shipped", 24.0 * n, best, med);
+    }
+    auto run_sc = [&](int tile, int S, int ctas, int target, int up, int down, int sh) {
+      const size_t smem = size_t(tile) * 8 * 2 * S + 8 * S;
+      if (smem > size_t(227 * 1024) / ctas - 1024) return;
+      CK(cudaFuncSetAttribute(ks, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+      int occ = 0;
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks, 256, smem));
+      if (occ < ctas) return;
+      const int grid = sms * ctas;
+      tm.run([&] { ks<<<grid, 256, smem>>>(a, b, c, 3.0, n, tile, S, target, up, down, sh, dbg_d); }, 2, 10, &best, &med);
+      CK(cudaGetLastError());
+      std::vector<int> ph(2 * grid);
+      CK(cudaMemcpy(ph.data(), dbg_d, sizeof(int) * 2 * grid, cudaMemcpyDeviceToHost));
+      double T = 0, o = 0;
+      for (int i = 0; i < grid; ++i) { T += ph[2 * i]; o += ph[2 * i + 1]; }
+      snprintf(param, sizeof param, "tileKB=%.1f S=%d ctas=%d target=%d up=%d down=%d ewma=%d T=%.0f outstanding=%.2f",
+               tile * 8 / 1024.0, S, ctas, target, up, down, sh, T / grid, o / grid / 100);
+      report("triad_selfclock", param, 24.0 * n, best, med);
+    };
+    for (int tile : {512, 1024})
+      for (int ctas : {1, 2})
+        for (int S : {6, 8})
+          for (int target : {2, 3, 4, 5})
+            for (int up : {1034, 1075})
+              for (int down : {1014, 973}) {
+                if (target >= S - 1) continue;
+                run_sc(tile, S, ctas, target, up, down, 4);
+              }
+  }
+
+  if (!strcmp(only, "hist")) {
+    double *sa, *sb2, *sc2;
+    int *pace_d;
+    CK(cudaMalloc(&sb2, n * 8)); CK(cudaMalloc(&sc2, n * 8)); CK(cudaMalloc(&sa, n * 8));
+    CK(cudaMalloc(&pace_d, sizeof(int) * (2 * 4096 + 16)));
+    CK(cudaMemset(sb2, 0, n * 8)); CK(cudaMemset(sc2, 0, n * 8));
+    a = sa; b = sb2; c = sc2;
+    auto ka = triad_tma_adapt;
+    for (int rep = 0; rep < 2; ++rep) {
+      tm.run([&] { int rc = gpu_probe_triad(a, b, c, 3.0, n, 1, nullptr); if (rc) exit(1); }, 2, 10, &best, &med);
+      report("triad_tma", "shipped", 24.0 * n, best, med);
+    }
+    for (int tile : {1024, 512}) {
+      const int S = 4, ctas = 2;
+      const size_t smem = size_t(tile) * 8 * 2 * S + 8 * S;
+      CK(cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+      const int grid = sms * ctas;
+      for (int p : {1900, 1950, 1975, 1990, 2000, 2010, 2025, 2050, 2100}) {
+        const int pace = p * tile / 1024;
+        CK(cudaMemset(pace_d + 8192, 0, sizeof(int) * 16));
+        tm.run([&] { ka<<<grid, 256, smem>>>(a, b, c, 3.0, n, tile, S, pace, 0, 0, 1 << 30, 1 << 30, 1, pace_d); }, 2, 10, &best, &med);
+        CK(cudaGetLastError());
+        int hist[8];
+        CK(cudaMemcpy(hist, pace_d + 8192, sizeof(hist), cudaMemcpyDeviceToHost));
+        double ht = 0;
+        for (int i = 0; i < 7; ++i) ht += hist[i];
+        snprintf(param, sizeof param, "tileKB=%.1f pace=%d hist<100:%.3f <200:%.3f <400:%.3f <800:%.3f <1600:%.3f <3200:%.3f >=3200:%.3f",
+                 tile * 8 / 1024.0, pace, hist[0] / ht, hist[1] / ht, hist[2] / ht, hist[3] / ht, hist[4] / ht, hist[5] / ht, hist[6] / ht);
+        report("triad_paced", param, 24.0 * n, best, med);
+      }
+    }
+  }
+
+  if (!strcmp(only, "ladder")) {
+    double *sa, *sb2, *sc2;
+    int *dbg_d;
+    CK(cudaMalloc(&sb2, n * 8)); CK(cudaMalloc(&sc2, n * 8)); CK(cudaMalloc(&sa, n * 8));
+    CK(cudaMalloc(&dbg_d, sizeof(int) * 2 * 4096));
+    CK(cudaMemset(sb2, 0, n * 8)); CK(cudaMemset(sc2, 0, n * 8));
+    a = sa; b = sb2; c = sc2;
+    auto kl = triad_tma_ladder;
+    for (int rep = 0; rep < 2; ++rep) {
+      tm.run([&] { int rc = gpu_probe_triad(a, b, c, 3.0, n, 1, nullptr); if (rc) exit(1); }, 2, 10, &best, &med);
+      report("triad_tma", "shipped", 24.0 * n, best, med);
+    }
+    auto run_l = [&](int tile, int S, int ctas, int pace0, int step, int stall_t, int bad_n, int win_n) {
+      const size_t smem = size_t(tile) * 8 * 2 * S + 8 * S;
+      CK(cudaFuncSetAttribute(kl, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+      const int grid = sms * ctas;
+      tm.run([&] { kl<<<grid, 256, smem>>>(a, b, c, 3.0, n, tile, S, pace0, step, stall_t, bad_n, win_n, dbg_d); }, 2, 10, &best, &med);
+      CK(cudaGetLastError());
+      std::vector<int> ph(2 * grid);
+      CK(cudaMemcpy(ph.data(), dbg_d, sizeof(int) * 2 * grid, cudaMemcpyDeviceToHost));
+      double pace = 0; int lmax = 0, l0 = 0;
+      for (int i = 0; i < grid; ++i) { pace += ph[2 * i]; lmax = std::max(lmax, ph[2 * i + 1]); l0 += ph[2 * i + 1] == 0; }
+      snprintf(param, sizeof param, "tileKB=%.1f S=%d ctas=%d pace0=%d step=%d stall_t=%d bad=%d/%d mean_final_pace=%.0f max_level=%d ctas_at_level0=%d",
+               tile * 8 / 1024.0, S, ctas, pace0, step, stall_t, bad_n, win_n, pace / grid, lmax, l0);
+      report("triad_ladder", param, 24.0 * n, best, med);
+    };
+    for (int pace0 : {1800, 1900, 1950, 1975, 1990, 2000, 2025})
+      for (int step : {20, 10}) run_l(1024, 4, 2, pace0, step, 800, 5, 64);
+    for (int pace0 : {1900, 1990}) {
+      run_l(1024, 4, 2, pace0, 20, 800, 3, 32);
+      run_l(1024, 4, 2, pace0, 20, 400, 8, 64);
+      run_l(1024, 4, 2, pace0, 30, 800, 5, 64);
+    }
+  }
+
+  if (!strcmp(only, "ladderns")) {
+    unsigned long long *gt;
+    CK(cudaMalloc(&gt, 8 * 80));
+    globaltimer_probe<<<1, 1>>>(gt);
+    unsigned long long gh[65];
+    CK(cudaMemcpy(gh, gt, sizeof(gh), cudaMemcpyDeviceToHost));
+    fprintf(stderr, "globaltimer increments (ns):");
+    for (int i = 0; i < 12; ++i) fprintf(stderr, " %llu", gh[i]);
+    unsigned long long tot = 0; for (int i = 0; i < 64; ++i) tot += gh[i];
+    fprintf(stderr, " ... 64 ticks = %llu ns = %llu cycles\n", tot, gh[64]);
+    double *sa, *sb2, *sc2;
+    int *dbg_d;
+    CK(cudaMalloc(&sb2, n * 8)); CK(cudaMalloc(&sc2, n * 8)); CK(cudaMalloc(&sa, n * 8));
+    CK(cudaMalloc(&dbg_d, sizeof(int) * 2 * 4096));
+    CK(cudaMemset(sb2, 0, n * 8)); CK(cudaMemset(sc2, 0, n * 8));
+    a = sa; b = sb2; c = sc2;
+    auto kl = triad_tma_ladder_ns;
+    for (int rep = 0; rep < 2; ++rep) {
+      tm.run([&] { int rc = gpu_probe_triad(a, b, c, 3.0, n, 1, nullptr); if (rc) exit(1); }, 2, 10, &best, &med);
+      report("triad_tma", "shipped", 24.0 * n, best, med);
+    }
+    const int tile = 1024, S = 4, ctas = 2;
+    const size_t smem = size_t(tile) * 8 * 2 * S + 8 * S;
+    CK(cudaFuncSetAttribute(kl, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    const int grid = sms * ctas;
+    for (int rep = 0; rep < 2; ++rep)
+      for (int pace_ns : {1000, 1008, 1013, 1018, 1023, 1030, 1040, 1055, 1070}) {
+        tm.run([&] { kl<<<grid, 256, smem>>>(a, b, c, 3.0, n, tile, S, pace_ns, 20, 800, 5, 64, dbg_d); }, 2, 20, &best, &med);
+        CK(cudaGetLastError());
+        std::vector<int> ph(2 * grid);
+        CK(cudaMemcpy(ph.data(), dbg_d, sizeof(int) * 2 * grid, cudaMemcpyDeviceToHost));
+        double pace = 0; int lmax = 0, l0 = 0;
+        for (int i = 0; i < grid; ++i) { pace += ph[2 * i]; lmax = std::max(lmax, ph[2 * i + 1]); l0 += ph[2 * i + 1] == 0; }
+        snprintf(param, sizeof param, "pace_ns=%d mean_final_pace_cycles=%.0f max_level=%d ctas_at_level0=%d", pace_ns, pace / grid, lmax, l0);
+        report("triad_ladder_ns", param, 24.0 * n, best, med);
+      }
   }
   CK(cudaFree(slab));
   return 0;

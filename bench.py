@@ -407,7 +407,9 @@ def run_ours(args, rank, local_rank, world):
             "roofline": {
                 "bound": "hbm", "kernel": "triad", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(ach / peak, 4), "peak_source": peak_src, "frac_of_nominal_8000": round(ach / 8000.0, 4),
-                "traffic": (traffic or {}).get("triad_dram_bytes_per_launch"),
+                "traffic": (traffic or {}).get("triad_paced_dram_bytes_per_launch_at_2^29" if gpuprobe.triad_pace_ns() > 0
+                                               else "triad_dram_bytes_per_launch"),
+                "kernel_variant": "triad_tma_paced<1024,4>" if gpuprobe.triad_pace_ns() > 0 else "triad_tma<512,4>",
                 "algorithmic_bytes_per_launch": BYTES_TRIAD * n,
                 "avg_launch_ms": round(t_avg, 4), "best_launch_ms": round(min(triad_ms), 4),
                 "triad_pace_ns": gpuprobe.triad_pace_ns(),  # AUTO's per-device calibration (> 0: paced TMA kernel)

@@ -72,7 +72,7 @@ int gpu_probe_init_fill(double *dst, uint64_t n, uint64_t first_index,
 /* K1  a[k] = fma(s, c[k], b[k]), one rounding.  24 bytes of HBM traffic per
  * element.  (slot: pods/nvidia-gpu-test-pod.yaml:9; spec: SURVEY 8d "Triad")
  * VARIANT_AUTO with n >= 2^26 and 16-byte-aligned pointers uses the paced TMA kernel at a
- * pace calibrated per device: the FIRST such call on a device [blocking] times 30 short
+ * pace calibrated per device: the FIRST such call on a device [blocking] times 27 short
  * launches on the caller's own buffers (harmless: the triad is idempotent) and synchronises
  * the stream once, about 25 ms, once per device per process -- make it before timing or
  * capturing (inside a stream capture AUTO silently uses the unpaced ring instead).

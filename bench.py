@@ -263,7 +263,12 @@ def run_ours(args, rank, local_rank, world):
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # Coordination (barriers, max over ranks, handle exchange) runs over gloo.  The NCCL
+        # communicator is created AFTER the timed HBM region: creating it costs every local
+        # HBM-streaming kernel 3.4 % on this stack (6904 -> 6693 GB/s triad, persists while the
+        # communicator lives, independent of NVLS/P2P/cuMem settings; tools/ablate_dist.py), and
+        # the probe's own collectives do not need it.  NCCL is the baseline of the sweep below.
+        dist.init_process_group("gloo")
 
     n = 1 << args.log2n
     first = shard_first_index(rank, n)  # each rank owns the shard [rank*n, (rank+1)*n) of one global index space
@@ -283,6 +288,26 @@ def run_ours(args, rank, local_rank, world):
         if dist is not None:
             dist.barrier()
 
+    def host_reduce(value, op):
+        """MAX / MIN over ranks of one float, over the gloo group (CPU tensors)."""
+        if dist is None:
+            return value
+        t = torch.tensor([value], dtype=torch.float64)
+        dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    nccl = {"group": None}
+
+    def nccl_group():
+        """Created on first use by ALL ranks at the same point (after the HBM region)."""
+        if nccl["group"] is None:
+            nccl["group"] = dist.new_group(backend="nccl", device_id=torch.device("cuda", local_rank))
+            warm = torch.ones(4, device="cuda")
+            dist.all_reduce(warm, group=nccl["group"])
+            torch.cuda.synchronize()
+            gpuprobe.triad_recalibrate()  # what the memory system sustains has just changed: pace again
+        return nccl["group"]
+
     # N > 1: the path's one collective (16 bytes of lanes).  Product path: fused into the
     # checksum kernel over NVLink peer stores (gpu_probe_checksum_u64_exchange); the mailbox
     # addresses travel between the ranks as CUDA IPC handles over torch.distributed.
@@ -291,16 +316,15 @@ def run_ours(args, rank, local_rank, world):
     if dist is not None and args.combine == "exchange":
         try:
             xchg = gpuprobe.Exchange(rank, world, 1 << args.sweep_log2max)  # payload: K4's allreduce operand
-            mine = torch.tensor(list(xchg.export_handle()), dtype=torch.uint8, device="cuda")
+            mine = torch.tensor(list(xchg.export_handle()), dtype=torch.uint8)
             allh = [torch.empty_like(mine) for _ in range(world)]
             dist.all_gather(allh, mine)
-            xchg.connect_ipc(b"".join(bytes(h.cpu().tolist()) for h in allh))
-            ok = torch.ones(1, dtype=torch.int32, device="cuda")
+            xchg.connect_ipc(b"".join(bytes(h.tolist()) for h in allh))
+            ok = 1.0
         except gpuprobe.ProbeError as e:
             print(f"bench.py: rank {rank}: CUDA IPC exchange unavailable ({e}); combining with NCCL", file=sys.stderr)
-            ok = torch.zeros(1, dtype=torch.int32, device="cuda")
-        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-        if int(ok.item()) == 0:
+            ok = 0.0
+        if host_reduce(ok, dist.ReduceOp.MIN) == 0.0:
             xchg = None
         combine = ("p2p_exchange_fused (gpu_probe_checksum_u64_exchange, CUDA IPC mailboxes)" if xchg is not None
                    else "nccl_allreduce_int64 (CUDA IPC unavailable on this box)")
@@ -324,7 +348,7 @@ def run_ours(args, rank, local_rank, world):
             ev[2].record()
         if dist is not None:  # wrapping int64 sum == wrapping u64 sum, bit for bit
             total.copy_(lanes)
-            dist.all_reduce(total)
+            dist.all_reduce(total, group=nccl_group())
 
     for _ in range(args.warmup):
         step()
@@ -355,15 +379,14 @@ def run_ours(args, rank, local_rank, world):
     per_rank = None
     if dist is not None:
         # every rank's own view of the timed region (rank 0 prints them: shows which GPU the others wait for)
-        mine_stats = torch.tensor([ms_total / args.steps, sum(triad_ms) / len(triad_ms), sum(csum_ms) / len(csum_ms)],
-                                  dtype=torch.float64, device="cuda")
+        mine_stats = torch.tensor([ms_total / args.steps, sum(triad_ms) / len(triad_ms), sum(csum_ms) / len(csum_ms),
+                                   float(gpuprobe.triad_pace_ns())], dtype=torch.float64)
         all_stats = [torch.empty_like(mine_stats) for _ in range(world)]
         dist.all_gather(all_stats, mine_stats)
         per_rank = [{"rank": r, "ms_per_step": round(float(v[0]), 4), "triad_ms": round(float(v[1]), 4),
-                     "checksum_incl_wait_ms": round(float(v[2]), 4)} for r, v in enumerate(all_stats)]
-        t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total = float(t.item())
+                     "checksum_incl_wait_ms": round(float(v[2]), 4), "triad_pace_ns": int(v[3])}
+                    for r, v in enumerate(all_stats)]
+        ms_total = host_reduce(ms_total, dist.ReduceOp.MAX)
         if xchg is not None:
             if xchg.status() != 0:
                 raise SystemExit(f"bench.py: rank {rank}: lanes exchange timed out")
@@ -378,9 +401,7 @@ def run_ours(args, rank, local_rank, world):
                 step(use_nccl=True)
             t_end.record()
             torch.cuda.synchronize()
-            t = torch.tensor([t_start.elapsed_time(t_end) / k2], dtype=torch.float64, device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            nccl_ms_step = float(t.item())
+            nccl_ms_step = host_reduce(t_start.elapsed_time(t_end) / k2, dist.ReduceOp.MAX)
             nccl_lanes = tuple(int(x) for x in total.cpu().numpy().view(np.uint64))
             if nccl_lanes != my_lanes:
                 raise SystemExit(f"bench.py: rank {rank}: exchange lanes {my_lanes} != NCCL lanes {nccl_lanes}")
@@ -392,7 +413,7 @@ def run_ours(args, rank, local_rank, world):
     e2e = None if args.no_e2e else run_e2e(args, gpuprobe, torch, b, c, n, first, rank_lanes, dist, world)
 
     # ---- NVLink part of the metric (N > 1): allreduce sweep, bus bandwidth ----
-    nvlink = run_allreduce_sweep(args, torch, dist, world, xchg, st) if dist is not None else None
+    nvlink = run_allreduce_sweep(args, torch, dist, world, xchg, st, nccl_group()) if dist is not None else None
 
     if rank == 0:
         peak, peak_src = measured_peak()
@@ -432,6 +453,9 @@ def run_ours(args, rank, local_rank, world):
         if dist is not None:
             line["per_rank"] = per_rank
             line["combine"] = {"how": combine, "ms_per_step_with_nccl_combine": nccl_ms_step,
+                               "note": "ranks coordinate over gloo; the NCCL communicator is created after the timed region "
+                                       "(creating it slows every local HBM kernel by ~3.4 % for as long as it lives, "
+                                       "tools/ablate_dist.py), so the NCCL-combine figure carries that cost",
                                "launches_per_step": 2 if xchg is not None else 4}
             line["gpu_launches"] = (2 if xchg is not None else 4) * args.steps
             # weak scaling over one global index space: the combined lanes have a known answer
@@ -496,7 +520,7 @@ def run_e2e(args, gpuprobe, torch, b, c, n, first, want_lanes, dist, world):
         raise SystemExit(f"bench.py: e2e lanes {got} differ from the resident path {want_lanes}")
     ms = dt / args.e2e_steps * 1e3
     if dist is not None:
-        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        t = torch.tensor([ms], dtype=torch.float64)  # gloo group: CPU tensor
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     gbs = (BYTES_TRIAD + BYTES_CHECKSUM) * ne * world / (ms / 1e3) / 1e9
@@ -507,7 +531,7 @@ def run_e2e(args, gpuprobe, torch, b, c, n, first, want_lanes, dist, world):
             "pcie_h2d_GBps": round(16 * ne / (ms / 1e3) / 1e9, 2)}
 
 
-def run_allreduce_sweep(args, torch, dist, world, xchg, st):
+def run_allreduce_sweep(args, torch, dist, world, xchg, st, nccl):
     """In-place fp32 sum allreduce, 1 KiB .. 1 GiB per rank; busbw = algbw * 2(G-1)/G.
     Two implementations on the same sizes: NCCL (torch.distributed) and the probe's own
     one-kernel allreduce over peer memory (gpu_probe_allreduce_f32, K4)."""
@@ -526,7 +550,7 @@ def run_allreduce_sweep(args, torch, dist, world, xchg, st):
             fn()
         e1.record()
         torch.cuda.synchronize()
-        t = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64, device="cuda")
+        t = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64)  # gloo: CPU tensor
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
         algbw = size / (ms / 1e3) / 1e9
@@ -546,7 +570,7 @@ def run_allreduce_sweep(args, torch, dist, world, xchg, st):
         view = buf[: size // 4]
         iters = 20 if size >= (1 << 20) else 50
         reps = 3 if size <= (4 << 20) else 1  # short series are noisy: keep the best of three
-        rows_nccl.append(min((series(lambda: dist.all_reduce(view), size, iters) for _ in range(reps)),
+        rows_nccl.append(min((series(lambda: dist.all_reduce(view, group=nccl), size, iters) for _ in range(reps)),
                              key=lambda r: r["us"]))
         buf.fill_(1.0)
         if xchg is not None:
@@ -567,7 +591,7 @@ def run_allreduce_sweep(args, torch, dist, world, xchg, st):
         gpuprobe.p2p_copy(out.data_ptr(), xchg.buffer, 4 * n_chk, st)
         torch.cuda.synchronize()
         want = (torch.arange(n_chk, device="cuda", dtype=torch.float32) % 7 + 1) * float(world * (world + 1) // 2)
-        ok = torch.tensor([int(torch.equal(out, want) and xchg.status() == 0)], dtype=torch.int32, device="cuda")
+        ok = torch.tensor([int(torch.equal(out, want) and xchg.status() == 0)], dtype=torch.int32)
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         if int(ok.item()) != 1:
             raise SystemExit(f"bench.py: rank {rank}: gpu_probe_allreduce_f32 result differs from the closed-form sum")

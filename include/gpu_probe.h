@@ -74,7 +74,7 @@ int gpu_probe_init_fill(double *dst, uint64_t n, uint64_t first_index,
  * VARIANT_AUTO with n >= 2^26 and 16-byte-aligned pointers uses the paced TMA kernel at a
  * pace calibrated per device: the FIRST such call on a device [blocking] times 27 short
  * launches on the caller's own buffers (harmless: the triad is idempotent) and synchronises
- * the stream once, about 25 ms, once per device per process -- make it before timing or
+ * the stream, about 50 ms, once per device per process -- make it before timing or
  * capturing (inside a stream capture AUTO silently uses the unpaced ring instead).
  * Environment: GPU_PROBE_TRIAD_PACE_NS=0 disables the paced kernel, =N fixes the pace. */
 int gpu_probe_triad(double *a, const double *b, const double *c, double s,
@@ -83,6 +83,11 @@ int gpu_probe_triad(double *a, const double *b, const double *c, double s,
 /* What VARIANT_AUTO's calibration decided for the current device: 0 = not calibrated yet,
  * < 0 = the unpaced ring is at least as fast here, > 0 = nanoseconds between a CTA's refills. */
 int gpu_probe_triad_pace_ns(void);
+
+/* Forget the current device's calibration: the next large VARIANT_AUTO triad calibrates again.
+ * For hosts that change what the memory system can sustain after the first call -- creating
+ * an NCCL communicator, for one, costs every local HBM kernel ~3.4 % on this stack. */
+int gpu_probe_triad_recalibrate(void);
 
 /* Bytes of device scratch the checksum kernels need (a constant). */
 size_t gpu_probe_checksum_workspace_bytes(void);

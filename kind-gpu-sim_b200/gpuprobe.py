@@ -118,6 +118,12 @@ def triad_pace_ns() -> int:
     return int(L.gpu_probe_triad_pace_ns())
 
 
+def triad_recalibrate() -> None:
+    L = lib()
+    L.gpu_probe_triad_recalibrate.restype = ctypes.c_int
+    _check(L.gpu_probe_triad_recalibrate(), "gpu_probe_triad_recalibrate")
+
+
 def workspace_bytes() -> int:
     return int(lib().gpu_probe_checksum_workspace_bytes())
 

@@ -21,6 +21,7 @@
 // No reference counterpart (slot: /root/reference/pods/nvidia-gpu-test-pod.yaml:9).
 #include "gpu_probe.h"
 
+#include <atomic>
 #include <cstdlib>
 #include <cstring>
 #include <cuda_runtime.h>
@@ -325,12 +326,15 @@ static int launch_allreduce(const AllreduceArgs &a, int algo, unsigned grid, cud
 using namespace probe;
 
 static int device_sms(int dev, int *sms) {
-  static int cache[64];
-  if (dev >= 0 && dev < 64 && cache[dev] > 0) { *sms = cache[dev]; return 0; }
+  static std::atomic<int> cache[64];
+  if (dev >= 0 && dev < 64) {
+    const int known = cache[dev].load(std::memory_order_relaxed);
+    if (known > 0) { *sms = known; return 0; }
+  }
   int v = 0;
   cudaError_t e = cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
   if (e != cudaSuccess) return int(e);
-  if (dev >= 0 && dev < 64) cache[dev] = v;
+  if (dev >= 0 && dev < 64) cache[dev].store(v, std::memory_order_relaxed);
   *sms = v;
   return 0;
 }

@@ -33,6 +33,8 @@
 #include <cstring>
 #include <cuda.h>
 #include <cuda_runtime.h>
+#include <atomic>
+#include <mutex>
 #include <new>
 #include <sys/socket.h>
 #include <sys/time.h>
@@ -76,6 +78,7 @@ struct DriverApi {
 };
 
 DriverApi g_drv;
+std::mutex g_drv_mutex;
 
 template <typename F>
 bool resolve(F *slot, const char *name) {
@@ -91,6 +94,7 @@ bool resolve(F *slot, const char *name) {
 
 // 0, or a CUDA error when there is no usable driver (e.g. a machine without a GPU).
 int driver(const DriverApi **out) {
+  std::lock_guard<std::mutex> lock(g_drv_mutex);  // set-up paths only; kernels are launched elsewhere
   if (g_drv.rc != 0) {
     cudaError_t e = cudaFree(nullptr);  // brings the runtime (and the driver under it) up on the current device
     if (e != cudaSuccess) return int(e);
@@ -424,7 +428,7 @@ extern "C" int gpu_probe_exchange_export(gpu_probe_exchange *x, unsigned char ha
   if (!live(x)) return GPU_PROBE_ENOTREADY;
   if (!handle) return GPU_PROBE_EINVAL;
   if (x->sock < 0) {
-    static int counter = 0;
+    static std::atomic<int> counter{0};
     int s = socket(AF_UNIX, SOCK_DGRAM | SOCK_CLOEXEC, 0);
     if (s < 0) return int(cudaErrorSystemNotReady);
     std::snprintf(x->sock_name, sizeof(x->sock_name), "gpuprobe-%d-%d-r%d", int(getpid()), ++counter, x->rank);

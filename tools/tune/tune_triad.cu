@@ -742,6 +742,39 @@ triad_tma_ladder_ns(double *__restrict__ a, const double *__restrict__ b, const 
   if (tid == 0 && dbg) { dbg[2 * blockIdx.x] = int(pace); dbg[2 * blockIdx.x + 1] = level; }
 }
 
+
+// Write-only stream with paced tiles: does smoothing help pure writes too?
+__global__ void __launch_bounds__(256)
+fill_paced(f64x2 *__restrict__ dst, uint64_t nvec, int tile_vecs, int pace_ns) {
+  const uint64_t ntiles = nvec / tile_vecs;
+  __shared__ long long go;
+  long long next_ok = 0, pace = (long long)pace_ns * 2, c0 = 0;
+  unsigned long long g0 = 0;
+  if (threadIdx.x == 0) { c0 = clock64(); g0 = global_ns(); next_ok = c0; }
+  uint64_t j = 0;
+  for (uint64_t t = blockIdx.x; t < ntiles; t += gridDim.x, ++j) {
+    if (pace_ns > 0) {
+      if (threadIdx.x == 0) {
+        if ((j & 63) == 63) {
+          const long long dg = (long long)(global_ns() - g0), dc = clock64() - c0;
+          if (dg > 20000) pace = (long long)pace_ns * dc / dg;
+        }
+        while (clock64() < next_ok) { }
+        next_ok += pace;
+        const long long now = clock64();
+        if (next_ok < now) next_ok = now;
+        go = now;
+      }
+      __syncthreads();
+    }
+    f64x2 *p = dst + t * tile_vecs;
+    for (int v = threadIdx.x; v < tile_vecs; v += 256) {
+      const uint64_t k = 2 * (t * tile_vecs + v);
+      st_stream(p + v, f64x2{unit_double(splitmix64_at(k, 1)), unit_double(splitmix64_at(k + 1, 1))});
+    }
+  }
+}
+
 int main(int argc, char **argv) {
   const int log2n = argc > 1 ? atoi(argv[1]) : 29;
   const char *only = argc > 2 ? argv[2] : "all";
@@ -1201,6 +1234,28 @@ int main(int argc, char **argv) {
         for (int i = 0; i < grid; ++i) { pace += ph[2 * i]; lmax = std::max(lmax, ph[2 * i + 1]); l0 += ph[2 * i + 1] == 0; }
         snprintf(param, sizeof param, "pace_ns=%d mean_final_pace_cycles=%.0f max_level=%d ctas_at_level0=%d", pace_ns, pace / grid, lmax, l0);
         report("triad_ladder_ns", param, 24.0 * n, best, med);
+      }
+  }
+
+  if (!strcmp(only, "fillpace")) {
+    double *sa;
+    CK(cudaMalloc(&sa, n * 8));
+    const uint64_t nvec = n / 2;
+    for (int rep = 0; rep < 2; ++rep) {
+      tm.run([&] { int rc = gpu_probe_init_fill(sa, n, 0, 1, nullptr); if (rc) exit(1); }, 2, 10, &best, &med);
+      report("init_fill", "shipped", 8.0 * n, best, med);
+    }
+    for (int ctas : {2, 4, 8})
+      for (int tile_kb : {4, 8, 16}) {
+        const int tile_vecs = tile_kb * 1024 / 16;
+        for (int gbs : {0, 6600, 6800, 7000, 7100, 7200, 7300, 7400}) {
+          // pace = time for one tile per CTA at the target aggregate rate
+          const int pace_ns = gbs ? int(double(tile_kb) * 1024 * sms * ctas / (gbs * 1e9) * 1e9) : 0;
+          tm.run([&] { fill_paced<<<sms * ctas, 256>>>(reinterpret_cast<f64x2 *>(sa), nvec, tile_vecs, pace_ns); }, 2, 10, &best, &med);
+          CK(cudaGetLastError());
+          snprintf(param, sizeof param, "ctas=%d tileKB=%d target_GBps=%d pace_ns=%d", ctas, tile_kb, gbs, pace_ns);
+          report("fill_paced", param, 8.0 * n, best, med);
+        }
       }
   }
   CK(cudaFree(slab));

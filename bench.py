@@ -392,7 +392,8 @@ def run_ours(args, rank, local_rank, world):
                 raise SystemExit(f"bench.py: rank {rank}: lanes exchange timed out")
             # the same step with the two-launch NCCL combine, for comparison only
             k2 = min(args.steps, 20)
-            for _ in range(3):
+            nccl_group()  # created here (and the triad pace forgotten): everything below runs with NCCL alive
+            for _ in range(12):  # first call re-calibrates the pace; a slow verdict is retried after 8 calls -- all untimed
                 step(use_nccl=True)
             barrier()
             torch.cuda.synchronize()

@@ -163,7 +163,19 @@ def cpu_pass_factory(n_sample: int):
     return one_pass, oracle.max_threads()
 
 
-def cpu_baseline(n_sample: int, repeats: int = 3):
+def cpu_baseline(n_sample: int, repeats: int = 3, threads: int = 0):
+    import oracle
+    all_threads = oracle.max_threads()
+    if threads:
+        oracle.set_threads(threads)
+    try:
+        return _cpu_baseline(n_sample, repeats)
+    finally:
+        if threads:
+            oracle.set_threads(all_threads)
+
+
+def _cpu_baseline(n_sample: int, repeats: int):
     one_pass, cores = cpu_pass_factory(n_sample)
     one_pass()  # first touch of a[]
     best = float("inf")
@@ -480,6 +492,7 @@ def run_ours(args, rank, local_rank, world):
             while log2s > 20 and avail and 3 * (8 << log2s) > 0.5 * avail:
                 log2s -= 1
             line["cpu_baseline"] = cpu_baseline(1 << log2s)
+            line["cpu_baseline_single_core"] = cpu_baseline(1 << min(log2s, 25), repeats=2, threads=1)
             if want != my_lanes:
                 print(json.dumps(line), flush=True)
                 raise SystemExit("bench.py: GPU lanes differ from the CPU oracle")

@@ -774,7 +774,10 @@ static int auto_triad_pace(double *a, const double *b, const double *c, double s
       return 0;  // never calibrate (and synchronise) inside a capture: ring kernel, calibrate another time
     }
     int rc = calibrate_triad_pace(a, b, c, s, n, st, dev);
-    if (rc) return rc;
+    if (rc) {  // calibration is an optimisation: if it cannot run, the unpaced ring can
+      cudaGetLastError();
+      g_pace_ns[dev].store(-1, std::memory_order_release);
+    }
     g_pace_attempts[dev].fetch_add(1, std::memory_order_relaxed);
     g_pace_calls[dev].store(0, std::memory_order_relaxed);
     p = g_pace_ns[dev].load(std::memory_order_acquire);

@@ -429,7 +429,7 @@ struct ChecksumTmaSmem {
 template <int TILE, int S>
 __global__ void __launch_bounds__(kThreads)
 checksum_tma(const uint64_t *__restrict__ w, uint64_t n, uint64_t first, uint64_t *__restrict__ out,
-             uint64_t *__restrict__ ws, const ExchangeArgs x) {
+             uint64_t *__restrict__ ws, const ExchangeArgs x, int pace_ns) {
   static_assert(TILE % (2 * kThreads) == 0, "tile must split into one u64x2 per thread per pass");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   uint64_t *sw = reinterpret_cast<uint64_t *>(smem_raw);
@@ -456,9 +456,17 @@ checksum_tma(const uint64_t *__restrict__ w, uint64_t n, uint64_t first, uint64_
     ++pj;
     if (++pst == S) pst = 0;
   };
+  // Paced refills (pace_ns > 0), as in triad_tma_paced but without its safety net: read-only
+  // traffic has no cliff.  Asking for more than HBM delivers degrades gently to what the plain
+  // ring gives (7318 GB/s); asking for ~7550 GB/s gives 7452 (tools/tune/tune_triad.cu csumpace).
+  long long next_ok = 0, pace = (long long)pace_ns * 2, c_start = 0;
+  unsigned long long g_start = 0;
   if (tid == 0) {
     policy = tma::policy_evict_first();
+    c_start = clock64();
+    g_start = global_ns();
     for (int i = 0; i < S && pj < my_tiles; ++i) issue();
+    next_ok = clock64() + pace;
   }
 
   Lanes acc{0, 0};
@@ -466,12 +474,24 @@ checksum_tma(const uint64_t *__restrict__ w, uint64_t n, uint64_t first, uint64_
   uint32_t parity = 0;
   uint64_t t = blockIdx.x;
   for (uint64_t j = 0; j < my_tiles; ++j, t += gridDim.x) {
+    if (tid == 0 && pace_ns > 0 && (j & 63) == 63) {  // cycles per nanosecond, refreshed
+      const long long dg = (long long)(global_ns() - g_start), dc = clock64() - c_start;
+      if (dg > 20000) pace = (long long)pace_ns * dc / dg;
+    }
     tma::mbar_wait(&full[st], parity);
     const u64x2 *pw = reinterpret_cast<const u64x2 *>(sw + size_t(st) * TILE);
 #pragma unroll
     for (int v = tid; v < TILE / 2; v += kThreads) lanes_vec(acc, pw[v], t * TILE + 2 * uint64_t(v));
     __syncthreads();  // every thread is done with slot st
-    if (tid == 0 && pj < my_tiles) issue();
+    if (tid == 0 && pj < my_tiles) {
+      if (pace_ns > 0) {
+        while (clock64() < next_ok) { }
+        next_ok += pace;
+        const long long now = clock64();
+        if (next_ok < now) next_ok = now;  // never bank credit
+      }
+      issue();
+    }
     if (++st == S) { st = 0; parity ^= 1u; }
   }
   if (blockIdx.x == gridDim.x - 1)
@@ -664,6 +684,10 @@ constexpr int kPacedTile = 1024, kPacedStages = 4, kPacedCtasPerSm = 2;
 constexpr int kPacedDefaultNs = 1040;          // explicit VARIANT_TMA_PACED without calibration: a conservative pace
 constexpr uint64_t kPacedMinElems = 1ull << 26;  // below 512 MiB per array the ring kernel is used: nothing to pace
 constexpr int kChecksumTile = 4096, kChecksumStages = 4, kChecksumCtasPerSm = 1;
+// One 32 KiB tile per SM per 650 ns = 7460 GB/s asked for.  Alone the checksum is fastest at 642 ns
+// (0.5819 ms against 0.5922 unpaced); right after a triad, with that kernel's dirty L2 lines still
+// draining, at 650-660 ns (0.6035-0.6042 ms against 0.6186).  GPU_PROBE_CHECKSUM_PACE_NS overrides, 0 = unpaced.
+constexpr int kChecksumPaceNs = 650;
 // LDG geometry from the same sweeps: mixed read/write traffic wants FEW resident CTAs
 // (triad: 2/SM with 8x16 B or 4x32 B loads per array per thread -> 6700 / 6530 GB/s;
 // 8/SM: 6100-6300), read-only wants more (checksum: 6/SM -> 7350 GB/s).
@@ -863,7 +887,8 @@ int checked_checksum(const uint64_t *w, uint64_t n, uint64_t first_index, uint64
     auto k = checksum_tma<kChecksumTile, kChecksumStages>;
     constexpr size_t smem = ChecksumTmaSmem<kChecksumTile, kChecksumStages>::kBytes;
     if ((rc = persistent_grid(k, smem, n / kChecksumTile, &grid, kChecksumCtasPerSm))) return rc;
-    k<<<grid, kThreads, smem, st>>>(w, n, first_index, out_lanes, ws, x);
+    static const int pace_ns = [] { const char *e = getenv("GPU_PROBE_CHECKSUM_PACE_NS"); return e ? atoi(e) : kChecksumPaceNs; }();
+    k<<<grid, kThreads, smem, st>>>(w, n, first_index, out_lanes, ws, x, n >= kPacedMinElems ? pace_ns : 0);
     return launch_rc();
   }
   if (variant == GPU_PROBE_VARIANT_LDG256 && aligned(w, 32)) {

@@ -775,6 +775,72 @@ fill_paced(f64x2 *__restrict__ dst, uint64_t nvec, int tile_vecs, int pace_ns) {
   }
 }
 
+
+// Read-only stream (the checksum's traffic) with paced refills: does smoothing help pure reads?
+__global__ void __launch_bounds__(256)
+csum_tma_paced(const uint64_t *__restrict__ w, uint64_t n, int tile, int S, int pace_ns, uint64_t *__restrict__ out) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  uint64_t *sw = reinterpret_cast<uint64_t *>(smem_raw);
+  uint64_t *full = sw + size_t(S) * tile;
+  const uint32_t tile_bytes = uint32_t(tile) * 8u;
+  const uint64_t ntiles = n / tile;
+  const uint64_t my_tiles = ntiles > blockIdx.x ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const int tid = threadIdx.x;
+  uint64_t policy = 0;
+  if (tid == 0) {
+    for (int i = 0; i < S; ++i) tma::mbar_init(&full[i], 1);
+    tma::fence_barrier_init();
+    policy = tma::policy_evict_first();
+  }
+  __syncthreads();
+  uint64_t pj = 0;
+  int pst = 0;
+  auto issue = [&]() {
+    const uint64_t t = blockIdx.x + pj * gridDim.x;
+    tma::mbar_arrive_expect_tx(&full[pst], tile_bytes);
+    tma::bulk_load(sw + size_t(pst) * tile, w + t * tile, tile_bytes, &full[pst], policy);
+    ++pj;
+    if (++pst == S) pst = 0;
+  };
+  long long next_ok = 0, pace = (long long)pace_ns * 2, c0 = 0;
+  unsigned long long g0 = 0;
+  if (tid == 0) {
+    c0 = clock64(); g0 = global_ns();
+    for (int i = 0; i < S && pj < my_tiles; ++i) issue();
+    next_ok = clock64() + pace;
+  }
+  uint64_t s0 = 0, s1 = 0;
+  int st = 0;
+  uint32_t parity = 0;
+  uint64_t t = blockIdx.x;
+  for (uint64_t j = 0; j < my_tiles; ++j, t += gridDim.x) {
+    if (tid == 0 && (j & 63) == 63) {
+      const long long dg = (long long)(global_ns() - g0), dc = clock64() - c0;
+      if (dg > 20000) pace = (long long)pace_ns * dc / dg;
+    }
+    tma::mbar_wait(&full[st], parity);
+    const u64x2 *pw = reinterpret_cast<const u64x2 *>(sw + size_t(st) * tile);
+#pragma unroll 4
+    for (int v = tid; v < tile / 2; v += 256) {
+      const u64x2 x = pw[v];
+      const uint64_t k = t * tile + 2 * uint64_t(v);
+      s0 += x.x + x.y; s1 += x.x * (2 * k + 1) + x.y * (2 * k + 3);
+    }
+    __syncthreads();
+    if (tid == 0 && pj < my_tiles) {
+      if (pace_ns > 0) {
+        while (clock64() < next_ok) { }
+        next_ok += pace;
+        const long long now = clock64();
+        if (next_ok < now) next_ok = now;
+      }
+      issue();
+    }
+    if (++st == S) { st = 0; parity ^= 1u; }
+  }
+  if (s0 == 0x1234567 && s1 == 0x7654321) out[0] = s0;  // keep the sums alive
+}
+
 int main(int argc, char **argv) {
   const int log2n = argc > 1 ? atoi(argv[1]) : 29;
   const char *only = argc > 2 ? argv[2] : "all";
@@ -1257,6 +1323,28 @@ int main(int argc, char **argv) {
           report("fill_paced", param, 8.0 * n, best, med);
         }
       }
+  }
+
+  if (!strcmp(only, "csumpace")) {
+    double *sa; uint64_t *o;
+    CK(cudaMalloc(&sa, n * 8)); CK(cudaMalloc(&o, 64));
+    CK(cudaMemset(sa, 1, n * 8));
+    auto kc = csum_tma_paced;
+    for (int tile_kb : {8, 16, 32})
+      for (int S : {4, 6})
+        for (int ctas : {1, 2}) {
+          const int tile = tile_kb * 128;
+          const size_t smem = size_t(tile) * 8 * S + 8 * S;
+          if (smem * ctas > 220 * 1024) continue;
+          CK(cudaFuncSetAttribute(kc, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+          for (int gbs : {0, 7200, 7350, 7450, 7550, 7650, 7800}) {
+            const int pace_ns = gbs ? int(double(tile_kb) * 1024 * sms * ctas / (gbs * 1e9) * 1e9) : 0;
+            tm.run([&] { kc<<<sms * ctas, 256, smem>>>(reinterpret_cast<const uint64_t *>(sa), n, tile, S, pace_ns, o); }, 2, 10, &best, &med);
+            CK(cudaGetLastError());
+            snprintf(param, sizeof param, "tileKB=%d S=%d ctas=%d target_GBps=%d pace_ns=%d", tile_kb, S, ctas, gbs, pace_ns);
+            report("csum_paced", param, 8.0 * n, best, med);
+          }
+        }
   }
   CK(cudaFree(slab));
   return 0;

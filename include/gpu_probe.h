@@ -97,6 +97,8 @@ size_t gpu_probe_checksum_workspace_bytes(void);
  * `workspace` is device scratch of gpu_probe_checksum_workspace_bytes() bytes,
  * zeroed ONCE by the caller after allocation (the kernel leaves it zeroed);
  * calls that overlap on the GPU must not share a workspace.
+ * For n >= 2^26 the TMA variant spaces its refills 650 ns apart (read-only traffic has no
+ * over-subscription cliff, so no calibration); GPU_PROBE_CHECKSUM_PACE_NS=0 disables, =N sets.
  * (slot: pods/nvidia-gpu-test-pod.yaml:9; spec: SURVEY 8d "Checksum") */
 int gpu_probe_checksum_u64(const uint64_t *w, uint64_t n, uint64_t first_index,
                            uint64_t *out_lanes, void *workspace, int variant,

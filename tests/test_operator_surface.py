@@ -35,11 +35,11 @@ exit 0
 '''
 
 
-@pytest.fixture()
-def shims(tmp_path):
+@pytest.fixture(params=[()], ids=["docker"])
+def shims(tmp_path, request):
     bindir = tmp_path / "bin"
     bindir.mkdir()
-    for tool in ("kind", "kubectl", "docker", "git", "nvidia-smi", "sleep", "pidof"):
+    for tool in ("kind", "kubectl", "docker", "git", "nvidia-smi", "sleep", "pidof") + tuple(request.param):
         p = bindir / tool
         p.write_text(SHIM)
         p.chmod(p.stat().st_mode | stat.S_IEXEC)
@@ -57,6 +57,24 @@ def shims(tmp_path):
         applied = [list(yaml.safe_load_all(f.read_text())) for f in sorted(tmp_path.glob("applied_*.yaml"))]
         return r, calls, [d for docs in applied for d in docs], work
     return run
+
+
+@pytest.mark.parametrize("shims", [("podman", "systemctl")], indirect=True, ids=["podman"])
+def test_podman_runtime_loads_images_as_archives(shims):
+    # reference behaviour with podman: no registry push; tag to localhost/, save, `kind load image-archive`
+    r, calls, applied, _ = shims("create", "nvidia")
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "Using Podman as container runtime" in r.stdout
+    assert any(c.startswith("podman build -t localhost:5000/nvidia-device-plugin:dev") for c in calls)
+    assert "podman tag localhost:5000/nvidia-device-plugin:dev localhost/nvidia-device-plugin:dev" in calls
+    assert "podman save localhost/nvidia-device-plugin:dev -o /tmp/image.tar" in calls
+    assert "kind load image-archive /tmp/image.tar --name kind-gpu-sim" in calls
+    assert not any(c.startswith(("podman push", "docker ")) for c in calls)
+    ds = next(d for d in applied if d["kind"] == "DaemonSet")
+    assert ds["spec"]["template"]["spec"]["containers"][0]["image"] == "localhost/nvidia-device-plugin:dev"
+    r, calls, _, _ = shims("load", "--image-name=localhost/gpu-probe:dev")
+    assert "podman save localhost/gpu-probe:dev -o /tmp/image.tar" in calls
+    assert "kind load image-archive /tmp/image.tar --name kind-gpu-sim" in calls
 
 
 def test_script_parses():

@@ -322,7 +322,8 @@ def run_ours(args, rank, local_rank, world):
 
     # N > 1: the path's one collective (16 bytes of lanes).  Product path: fused into the
     # checksum kernel over NVLink peer stores (gpu_probe_checksum_u64_exchange); the mailbox
-    # addresses travel between the ranks as CUDA IPC handles over torch.distributed.
+    # segments reach the other ranks as 64-byte handles over torch.distributed (gloo); underneath,
+    # gpu_probe_exchange_connect_ipc passes VMM file descriptors over unix sockets.
     # NCCL (int64 allreduce after K2) is timed beside it as the two-launch baseline.
     xchg, combine = None, "none (single GPU)"
     if dist is not None and args.combine == "exchange":
@@ -334,12 +335,12 @@ def run_ours(args, rank, local_rank, world):
             xchg.connect_ipc(b"".join(bytes(h.tolist()) for h in allh))
             ok = 1.0
         except gpuprobe.ProbeError as e:
-            print(f"bench.py: rank {rank}: CUDA IPC exchange unavailable ({e}); combining with NCCL", file=sys.stderr)
+            print(f"bench.py: rank {rank}: cross-process exchange unavailable ({e}); combining with NCCL", file=sys.stderr)
             ok = 0.0
         if host_reduce(ok, dist.ReduceOp.MIN) == 0.0:
             xchg = None
-        combine = ("p2p_exchange_fused (gpu_probe_checksum_u64_exchange, CUDA IPC mailboxes)" if xchg is not None
-                   else "nccl_allreduce_int64 (CUDA IPC unavailable on this box)")
+        combine = ("p2p_exchange_fused (gpu_probe_checksum_u64_exchange; segments shared across processes as VMM file descriptors)" if xchg is not None
+                   else "nccl_allreduce_int64 (cross-process segments unavailable on this box)")
         dist.barrier()
     elif dist is not None:
         combine = "nccl_allreduce_int64"

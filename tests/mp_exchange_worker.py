@@ -1,6 +1,6 @@
 """Worker for tests/test_gpu_exchange.py::test_exchange_across_processes_over_ipc.
 
-Launched by torchrun, one process per GPU.  The ranks trade CUDA IPC handles of their
+Launched by torchrun, one process per GPU.  The ranks trade the 64-byte handles of their
 mailboxes over gloo (host plumbing only), then run the fused checksum + lanes exchange
 and the fused triad + checksum + exchange; every rank checks the result against the
 CPU oracle of the WHOLE buffer."""

@@ -194,7 +194,7 @@ def test_exchange_argument_and_state_errors():
     assert L.gpu_probe_exchange_destroy(None) == gpuprobe.ENOTREADY
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs: one process per GPU over CUDA IPC")
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs: one process per GPU, segments passed as file descriptors")
 def test_exchange_across_processes_over_ipc():
     world = min(torch.cuda.device_count(), 8)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",

@@ -380,6 +380,7 @@ def run_ours(args, rank, local_rank, world):
         torch.cuda.synchronize()
     barrier()
     ms_total = t_start.elapsed_time(t_end)
+    pace_timed = gpuprobe.triad_pace_ns()  # as used in the timed region (creating NCCL later re-calibrates)
     triad_ms = [e[0].elapsed_time(e[1]) for e in evs]
     csum_ms = [e[1].elapsed_time(e[2]) for e in evs]
     # this rank's own shard lanes (untimed; the exchange path only ever holds the combined ones)
@@ -393,7 +394,7 @@ def run_ours(args, rank, local_rank, world):
     if dist is not None:
         # every rank's own view of the timed region (rank 0 prints them: shows which GPU the others wait for)
         mine_stats = torch.tensor([ms_total / args.steps, sum(triad_ms) / len(triad_ms), sum(csum_ms) / len(csum_ms),
-                                   float(gpuprobe.triad_pace_ns())], dtype=torch.float64)
+                                   float(pace_timed)], dtype=torch.float64)
         all_stats = [torch.empty_like(mine_stats) for _ in range(world)]
         dist.all_gather(all_stats, mine_stats)
         per_rank = [{"rank": r, "ms_per_step": round(float(v[0]), 4), "triad_ms": round(float(v[1]), 4),
@@ -442,12 +443,12 @@ def run_ours(args, rank, local_rank, world):
             "roofline": {
                 "bound": "hbm", "kernel": "triad", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(ach / peak, 4), "peak_source": peak_src, "frac_of_nominal_8000": round(ach / 8000.0, 4),
-                "traffic": (traffic or {}).get("triad_paced_dram_bytes_per_launch_at_2^29" if gpuprobe.triad_pace_ns() > 0
+                "traffic": (traffic or {}).get("triad_paced_dram_bytes_per_launch_at_2^29" if pace_timed > 0
                                                else "triad_dram_bytes_per_launch"),
-                "kernel_variant": "triad_tma_paced<1024,4>" if gpuprobe.triad_pace_ns() > 0 else "triad_tma<512,4>",
+                "kernel_variant": "triad_tma_paced<1024,4>" if pace_timed > 0 else "triad_tma<512,4>",
                 "algorithmic_bytes_per_launch": BYTES_TRIAD * n,
                 "avg_launch_ms": round(t_avg, 4), "best_launch_ms": round(min(triad_ms), 4),
-                "triad_pace_ns": gpuprobe.triad_pace_ns(),  # AUTO's per-device calibration (> 0: paced TMA kernel)
+                "triad_pace_ns": pace_timed,  # AUTO's per-device calibration (> 0: paced TMA kernel)
             },
             "kernels": {
                 "triad": {"bytes": BYTES_TRIAD * n, "avg_ms": round(t_avg, 4), "best_ms": round(min(triad_ms), 4),

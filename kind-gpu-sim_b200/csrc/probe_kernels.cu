@@ -534,7 +534,7 @@ copy_vec(uint4 *__restrict__ dst, const uint4 *__restrict__ src, uint64_t nvec, 
 // (cp.async.bulk.wait_group.read).
 template <int TILE_BYTES, int S>
 __global__ void __launch_bounds__(32)
-copy_tma(unsigned char *__restrict__ dst, const unsigned char *__restrict__ src, uint64_t bytes) {
+copy_tma(unsigned char *__restrict__ dst, const unsigned char *__restrict__ src, uint64_t bytes, int pace_ns) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + size_t(S) * TILE_BYTES);
   const uint64_t ntiles = bytes / TILE_BYTES;
@@ -549,16 +549,35 @@ copy_tma(unsigned char *__restrict__ dst, const unsigned char *__restrict__ src,
       tma::mbar_arrive_expect_tx(&full[st], TILE_BYTES);
       tma::bulk_load(smem_raw + size_t(st) * TILE_BYTES, src + t * TILE_BYTES, TILE_BYTES, &full[st], policy);
     };
+    // Refills are spaced pace_ns apart (0: as fast as stages free up).  With only S = 3 stages behind
+    // it, asking for more than HBM sustains degrades gently (7200 GB/s asked: 6430, the unpaced ring:
+    // 6546), while 6800 GB/s asked gives 6750-6760 (tools/tune/tune_triad.cu copypace).
+    long long pace = (long long)pace_ns * 2, next_ok = 0;
+    const long long c_start = clock64();
+    const unsigned long long g_start = global_ns();
     for (uint64_t j = 0; j < uint64_t(S - 1) && j < my_tiles; ++j) load(j);
+    next_ok = clock64() + pace;
     for (uint64_t j = 0; j < my_tiles; ++j) {
       const int st = int(j % S);
       const uint64_t t = blockIdx.x + j * gridDim.x;
+      if (pace_ns > 0 && (j & 63) == 63) {  // cycles per nanosecond, refreshed
+        const long long dg = (long long)(global_ns() - g_start), dc = clock64() - c_start;
+        if (dg > 20000) pace = (long long)pace_ns * dc / dg;
+      }
       tma::mbar_wait(&full[st], uint32_t(j / S) & 1u);
       tma::bulk_store(dst + t * TILE_BYTES, smem_raw + size_t(st) * TILE_BYTES, TILE_BYTES);
       tma::bulk_commit();
       // stage (j-1)%S == (j+S-1)%S is free once store j-1 has read it: refill it with tile j+S-1
       tma::bulk_wait_read<1>();
-      if (j + S - 1 < my_tiles) load(j + S - 1);
+      if (j + S - 1 < my_tiles) {
+        if (pace_ns > 0) {
+          while (clock64() < next_ok) { }
+          next_ok += pace;
+          const long long now = clock64();
+          if (next_ok < now) next_ok = now;  // never bank credit
+        }
+        load(j + S - 1);
+      }
     }
     tma::bulk_wait_all<0>();
   }
@@ -692,6 +711,7 @@ constexpr int kChecksumPaceNs = 650;
 // (triad: 2/SM with 8x16 B or 4x32 B loads per array per thread -> 6700 / 6530 GB/s;
 // 8/SM: 6100-6300), read-only wants more (checksum: 6/SM -> 7350 GB/s).
 constexpr int kCopyTileBytes = 32 * 1024, kCopyStages = 3;
+constexpr int kCopyPaceNs = 1426;  // one 32 KiB tile (64 KiB of traffic) per SM per 1426 ns = 6800 GB/s asked for; GPU_PROBE_COPY_PACE_NS=0: unpaced
 constexpr int kLdgTriadCtasPerSm = 2;
 constexpr int kLdgChecksumCtasPerSm = 6;
 
@@ -1042,7 +1062,8 @@ int gpu_probe_p2p_copy(void *dst, const void *src, uint64_t bytes, void *stream)
     if ((rc = kernel_facts(reinterpret_cast<const void *>(k), smem, 32, &occ, &sms))) return rc;
     uint64_t g = uint64_t(sms), tiles = bytes / kCopyTileBytes;
     if (g > tiles) g = tiles;
-    k<<<unsigned(g), 32, smem, st>>>(static_cast<unsigned char *>(dst), static_cast<const unsigned char *>(src), bytes);
+    static const int pace_ns = [] { const char *e = getenv("GPU_PROBE_COPY_PACE_NS"); return e ? atoi(e) : kCopyPaceNs; }();
+    k<<<unsigned(g), 32, smem, st>>>(static_cast<unsigned char *>(dst), static_cast<const unsigned char *>(src), bytes, pace_ns);
     return launch_rc();
   }
   if (aligned(dst, 16) && aligned(src, 16)) {

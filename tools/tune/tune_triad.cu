@@ -841,6 +841,54 @@ csum_tma_paced(const uint64_t *__restrict__ w, uint64_t n, int tile, int S, int 
   if (s0 == 0x1234567 && s1 == 0x7654321) out[0] = s0;  // keep the sums alive
 }
 
+
+// K3 as a paced DMA pipeline (see copy_tma in probe_kernels.cu): one thread, bulk load -> bulk store.
+__global__ void __launch_bounds__(32)
+copy_tma_paced(unsigned char *__restrict__ dst, const unsigned char *__restrict__ src, uint64_t bytes, int tile_bytes, int S,
+               int pace_ns) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + size_t(S) * tile_bytes);
+  const uint64_t ntiles = bytes / tile_bytes;
+  const uint64_t my_tiles = ntiles > blockIdx.x ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  if (threadIdx.x != 0) return;
+  for (int i = 0; i < S; ++i) tma::mbar_init(&full[i], 1);
+  tma::fence_barrier_init();
+  const uint64_t policy = tma::policy_evict_first();
+  auto load = [&](uint64_t j) {
+    const int st = int(j % S);
+    const uint64_t t = blockIdx.x + j * gridDim.x;
+    tma::mbar_arrive_expect_tx(&full[st], tile_bytes);
+    tma::bulk_load(smem_raw + size_t(st) * tile_bytes, src + t * tile_bytes, tile_bytes, &full[st], policy);
+  };
+  long long pace = (long long)pace_ns * 2, next_ok = 0;
+  const long long c0 = clock64();
+  const unsigned long long g0 = global_ns();
+  for (uint64_t j = 0; j < uint64_t(S - 1) && j < my_tiles; ++j) load(j);
+  next_ok = clock64() + pace;
+  for (uint64_t j = 0; j < my_tiles; ++j) {
+    const int st = int(j % S);
+    const uint64_t t = blockIdx.x + j * gridDim.x;
+    if ((j & 63) == 63) {
+      const long long dg = (long long)(global_ns() - g0), dc = clock64() - c0;
+      if (dg > 20000) pace = (long long)pace_ns * dc / dg;
+    }
+    tma::mbar_wait(&full[st], uint32_t(j / S) & 1u);
+    tma::bulk_store(dst + t * tile_bytes, smem_raw + size_t(st) * tile_bytes, tile_bytes);
+    tma::bulk_commit();
+    tma::bulk_wait_read<1>();
+    if (j + S - 1 < my_tiles) {
+      if (pace_ns > 0) {
+        while (clock64() < next_ok) { }
+        next_ok += pace;
+        const long long now = clock64();
+        if (next_ok < now) next_ok = now;
+      }
+      load(j + S - 1);
+    }
+  }
+  tma::bulk_wait_all<0>();
+}
+
 int main(int argc, char **argv) {
   const int log2n = argc > 1 ? atoi(argv[1]) : 29;
   const char *only = argc > 2 ? argv[2] : "all";
@@ -1345,6 +1393,31 @@ int main(int argc, char **argv) {
             report("csum_paced", param, 8.0 * n, best, med);
           }
         }
+  }
+
+  if (!strcmp(only, "copypace")) {
+    unsigned char *src, *dst;
+    const uint64_t bytes = n * 8;
+    CK(cudaMalloc(&src, bytes)); CK(cudaMalloc(&dst, bytes));
+    CK(cudaMemset(src, 3, bytes));
+    auto kc = copy_tma_paced;
+    for (int rep = 0; rep < 2; ++rep) {
+      tm.run([&] { int rc = gpu_probe_p2p_copy(dst, src, bytes, nullptr); if (rc) exit(1); }, 2, 10, &best, &med);
+      report("copy", "shipped", 2.0 * bytes, best, med);
+    }
+    for (int tile_kb : {16, 32})
+      for (int S : {3, 4, 6}) {
+        const size_t smem = size_t(tile_kb) * 1024 * S + 8 * S;
+        if (smem > 200 * 1024) continue;
+        CK(cudaFuncSetAttribute(kc, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        for (int gbs : {0, 6400, 6600, 6800, 6900, 7000, 7100, 7200}) {
+          const int pace_ns = gbs ? int(2.0 * tile_kb * 1024 * sms / (gbs * 1e9) * 1e9) : 0;
+          tm.run([&] { kc<<<sms, 32, smem>>>(dst, src, bytes, tile_kb * 1024, S, pace_ns); }, 2, 10, &best, &med);
+          CK(cudaGetLastError());
+          snprintf(param, sizeof param, "tileKB=%d S=%d target_GBps=%d pace_ns=%d", tile_kb, S, gbs, pace_ns);
+          report("copy_paced", param, 2.0 * bytes, best, med);
+        }
+      }
   }
   CK(cudaFree(slab));
   return 0;

@@ -163,8 +163,14 @@ def cpu_pass_factory(n_sample: int):
     return one_pass, oracle.max_threads()
 
 
+def host_cores() -> int:
+    return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+
+
 def cpu_baseline(n_sample: int, repeats: int = 3, threads: int = 0):
     import oracle
+    if not threads and oracle.max_threads() < host_cores():
+        oracle.set_threads(host_cores())  # a launcher (torchrun) pinned OMP_NUM_THREADS=1: this leg runs on rank 0 alone
     all_threads = oracle.max_threads()
     if threads:
         oracle.set_threads(threads)
@@ -186,7 +192,7 @@ def _cpu_baseline(n_sample: int, repeats: int):
     gbs = (BYTES_TRIAD + BYTES_CHECKSUM) * n_sample / best / 1e9
     return {"value": round(gbs, 3), "unit": "GB/s", "cores": cores, "kind": "port",
             "sample": f"oracle/probe_ref.c array mode, triad+checksum over 2^{n_sample.bit_length() - 1} fp64 elements "
-                      f"per array (of 2^29), best of {repeats}, OpenMP x{cores}"}
+                      f"per array (of 2^29), best of {repeats}, OpenMP x{cores} of {host_cores()} host cores"}
 
 
 def run_reference(args, rank: int):
@@ -198,6 +204,10 @@ def run_reference(args, rank: int):
     while args.ref_log2n > 20 and avail and 3 * (8 << args.ref_log2n) > 0.5 * avail:
         args.ref_log2n -= 1
     n_sample = 1 << args.ref_log2n
+    import oracle
+    # torchrun exports OMP_NUM_THREADS=1 to every rank; rank 0 is the only rank that computes here,
+    # so it takes all the host's cores back (what the N=1 launch gets by default)
+    oracle.set_threads(host_cores())
     one_pass, cores = cpu_pass_factory(n_sample)
     for _ in range(max(args.warmup, 1)):
         one_pass()
@@ -208,7 +218,8 @@ def run_reference(args, rank: int):
     ms = dt / args.steps * 1e3
     gbs = (BYTES_TRIAD + BYTES_CHECKSUM) * n_sample / (ms / 1e3) / 1e9
     sample = (f"oracle/probe_ref.c array mode (CPU port; the reference's own slot is `echo`), triad+checksum over "
-              f"2^{args.ref_log2n} fp64 elements per array per step (bounded sample of the 2^29 workload), OpenMP x{cores}")
+              f"2^{args.ref_log2n} fp64 elements per array per step "
+              f"({'the whole 2^29 workload' if args.ref_log2n >= 29 else 'bounded sample of the 2^29 workload'}), OpenMP x{cores}")
     line = {
         "impl": "reference", "metric": METRIC, "value": round(gbs, 3), "unit": "GB/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 4), "higher_is_better": True,
@@ -308,6 +319,12 @@ def run_ours(args, rank, local_rank, world):
         dist.all_reduce(t, op=op)
         return float(t.item())
 
+    def calibrate():
+        """The ONLY blocking part of AUTO's pacing, made explicitly and outside every timed region."""
+        if variant == gpuprobe.VARIANT_AUTO:
+            gpuprobe.triad_calibrate(a.data_ptr(), b.data_ptr(), c.data_ptr(), n, st)
+        return gpuprobe.triad_pace_ns()
+
     nccl = {"group": None}
 
     def nccl_group():
@@ -317,7 +334,7 @@ def run_ours(args, rank, local_rank, world):
             warm = torch.ones(4, device="cuda")
             dist.all_reduce(warm, group=nccl["group"])
             torch.cuda.synchronize()
-            gpuprobe.triad_recalibrate()  # what the memory system sustains has just changed: pace again
+            calibrate()  # what the memory system sustains has just changed: pace again (blocking, untimed)
         return nccl["group"]
 
     # N > 1: the path's one collective (16 bytes of lanes).  Product path: fused into the
@@ -363,6 +380,7 @@ def run_ours(args, rank, local_rank, world):
             total.copy_(lanes)
             dist.all_reduce(total, group=nccl_group())
 
+    pace_first = calibrate()
     for _ in range(args.warmup):
         step()
     torch.cuda.synchronize()
@@ -394,11 +412,16 @@ def run_ours(args, rank, local_rank, world):
     if dist is not None:
         # every rank's own view of the timed region (rank 0 prints them: shows which GPU the others wait for)
         mine_stats = torch.tensor([ms_total / args.steps, sum(triad_ms) / len(triad_ms), sum(csum_ms) / len(csum_ms),
-                                   float(pace_timed)], dtype=torch.float64)
+                                   float(pace_timed), statistics.median(triad_ms), max(triad_ms), float(pace_first)],
+                                  dtype=torch.float64)
         all_stats = [torch.empty_like(mine_stats) for _ in range(world)]
         dist.all_gather(all_stats, mine_stats)
         per_rank = [{"rank": r, "ms_per_step": round(float(v[0]), 4), "triad_ms": round(float(v[1]), 4),
-                     "checksum_incl_wait_ms": round(float(v[2]), 4), "triad_pace_ns": int(v[3])}
+                     "triad_ms_median": round(float(v[4]), 4), "triad_ms_max": round(float(v[5]), 4),
+                     "checksum_incl_wait_ms": round(float(v[2]), 4), "triad_pace_ns": int(v[3]),
+                     # a GPU whose calibration lands at the slow end of the ladder (or on "ring") sustains ~5 % less HBM
+                     # bandwidth than its neighbours: seen on GPUs another multi-GPU process used moments before
+                     "slow_state": bool(int(v[6]) < 0 or int(v[6]) >= 1052)}
                     for r, v in enumerate(all_stats)]
         ms_total = host_reduce(ms_total, dist.ReduceOp.MAX)
         if xchg is not None:
@@ -407,7 +430,7 @@ def run_ours(args, rank, local_rank, world):
             # the same step with the two-launch NCCL combine, for comparison only
             k2 = min(args.steps, 20)
             nccl_group()  # created here (and the triad pace forgotten): everything below runs with NCCL alive
-            for _ in range(12):  # first call re-calibrates the pace; a slow verdict is retried after 8 calls -- all untimed
+            for _ in range(max(args.warmup, 3)):
                 step(use_nccl=True)
             barrier()
             torch.cuda.synchronize()
@@ -448,13 +471,17 @@ def run_ours(args, rank, local_rank, world):
                 "kernel_variant": "triad_tma_paced<1024,4>" if pace_timed > 0 else "triad_tma<512,4>",
                 "algorithmic_bytes_per_launch": BYTES_TRIAD * n,
                 "avg_launch_ms": round(t_avg, 4), "best_launch_ms": round(min(triad_ms), 4),
-                "triad_pace_ns": pace_timed,  # AUTO's per-device calibration (> 0: paced TMA kernel)
+                "median_launch_ms": round(statistics.median(triad_ms), 4), "max_launch_ms": round(max(triad_ms), 4),
+                "triad_pace_ns": pace_timed,  # gpu_probe_triad_calibrate's verdict (> 0: paced TMA kernel; -2: drift guard fired)
+                "slow_state": bool(pace_first < 0 or pace_first >= 1052),
             },
             "kernels": {
                 "triad": {"bytes": BYTES_TRIAD * n, "avg_ms": round(t_avg, 4), "best_ms": round(min(triad_ms), 4),
+                          "median_ms": round(statistics.median(triad_ms), 4), "max_ms": round(max(triad_ms), 4),
                           "GBps_avg": round(ach, 1), "frac_measured_peak": round(ach / peak, 4)},
                 "checksum_u64": {"bytes": BYTES_CHECKSUM * n, "avg_ms": round(c_avg, 4),
                                  "best_ms": round(min(csum_ms), 4),
+                                 "median_ms": round(statistics.median(csum_ms), 4), "max_ms": round(max(csum_ms), 4),
                                  "GBps_avg": round(BYTES_CHECKSUM * n / (c_avg / 1e3) / 1e9, 1),
                                  "frac_measured_peak": round(BYTES_CHECKSUM * n / (c_avg / 1e3) / 1e9 / peak, 4)},
             },
@@ -635,15 +662,15 @@ def main():
     ap.add_argument("--e2e-log2n", type=int, default=29)
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--e2e-warmup", type=int, default=1)
-    ap.add_argument("--cpu-log2n", type=int, default=28, help="cpu_baseline sample size (elements per array)")
-    ap.add_argument("--ref-log2n", type=int, default=28, help="--impl reference sample per step")
+    ap.add_argument("--cpu-log2n", type=int, default=29, help="cpu_baseline sample size (elements per array; halved while 3 arrays exceed half of MemAvailable)")
+    ap.add_argument("--ref-log2n", type=int, default=29, help="--impl reference elements per array per step (same fallback)")
     ap.add_argument("--sweep-log2max", type=int, default=30)
     ap.add_argument("--combine", choices=["exchange", "nccl"], default="exchange",
                     help="N>1: how the 16-byte lanes are summed over ranks (fused P2P exchange, or NCCL)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / parity leg")
     ap.add_argument("--no-clocks", action="store_true", help="ablation only: do not sample NVML clocks while timing")
-    ap.add_argument("--clock-period-ms", type=float, default=100.0, help="NVML sampling period during the timed region")
+    ap.add_argument("--clock-period-ms", type=float, default=5.0, help="NVML sampling period during the timed region")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3  # timing rule: at least 3 warm-up steps

@@ -71,22 +71,50 @@ int gpu_probe_init_fill(double *dst, uint64_t n, uint64_t first_index,
 
 /* K1  a[k] = fma(s, c[k], b[k]), one rounding.  24 bytes of HBM traffic per
  * element.  (slot: pods/nvidia-gpu-test-pod.yaml:9; spec: SURVEY 8d "Triad")
- * VARIANT_AUTO with n >= 2^26 and 16-byte-aligned pointers uses the paced TMA kernel at a
- * pace calibrated per device: the FIRST such call on a device [blocking] times 27 short
- * launches on the caller's own buffers (harmless: the triad is idempotent) and synchronises
- * the stream, about 50 ms, once per device per process -- make it before timing or
- * capturing (inside a stream capture AUTO silently uses the unpaced ring instead).
+ * Asynchronous for every variant, AUTO included: it never synchronises, times or calibrates
+ * anything.  VARIANT_AUTO runs the TMA ring; on a device that gpu_probe_triad_calibrate() has
+ * calibrated it runs the paced TMA kernel (n >= 2^26, 16-byte-aligned pointers) at that
+ * device's pace instead, +3-4 % on this fleet.
  * Environment: GPU_PROBE_TRIAD_PACE_NS=0 disables the paced kernel, =N fixes the pace. */
 int gpu_probe_triad(double *a, const double *b, const double *c, double s,
                     uint64_t n, int variant, void *stream);
 
-/* What VARIANT_AUTO's calibration decided for the current device: 0 = not calibrated yet,
- * < 0 = the unpaced ring is at least as fast here, > 0 = nanoseconds between a CTA's refills. */
+/* [blocking, ALLOCATES 64 bytes of pinned host memory on a device's first calibration]
+ * Finds the pace of the paced triad for the CURRENT device: 27 timed launches of the paced
+ * kernel over min(n, 2^29) elements of the caller's own buffers plus a stream synchronise,
+ * about 50 ms.  a[] is overwritten (with the triad for s = GPU_PROBE_SCALAR); b[] and c[] are
+ * only read, and a[] must not overlap either of them (GPU_PROBE_EINVAL) -- an in-place triad
+ * cannot be replayed.  Not inside a stream capture (cudaErrorStreamCaptureUnsupported).
+ * With n < 2^26 or pointers that are not 16-byte aligned there is nothing to calibrate (AUTO
+ * never paces such calls): returns 0 and changes nothing.
+ * Call it once per device before the timed or captured part of the program -- and again after
+ * anything that changes what the memory system sustains (creating an NCCL communicator costs
+ * every local HBM kernel ~3.4 % on this stack).  Nothing else in this library ever runs a
+ * calibration: a device that was never calibrated simply keeps the unpaced ring.
+ * Do not launch other work on the device while it runs; calibrations of one device from
+ * several threads are serialised.
+ * Drift guard: every paced AUTO launch measures itself on the device, and its last CTA leaves the
+ * verdict in that pinned host block, which the next call reads with a plain load (no
+ * synchronisation).  After 3 launches in a row that took more than 1.04 x (tiles per CTA x pace)
+ * + 10 us -- the memory system sustains less than when the device was calibrated -- AUTO goes
+ * back to the ring on that device until it is calibrated again.  Paced AUTO launches that
+ * overlap on one device share that record and may trip the guard early; that costs speed only. */
+int gpu_probe_triad_calibrate(double *a, const double *b, const double *c, uint64_t n,
+                              void *stream);
+
+/* State of VARIANT_AUTO's pacing on the current device: 0 = never calibrated (ring), -1 =
+ * calibrated, the unpaced ring is at least as fast here, -2 = calibrated, then sent back to the
+ * ring by the drift guard, > 0 = nanoseconds between a CTA's refills. */
 int gpu_probe_triad_pace_ns(void);
 
-/* Forget the current device's calibration: the next large VARIANT_AUTO triad calibrates again.
- * For hosts that change what the memory system can sustain after the first call -- creating
- * an NCCL communicator, for one, costs every local HBM kernel ~3.4 % on this stack. */
+/* What the drift guard last saw on the current device, read from the pinned host block without
+ * synchronising (so it describes the most recent paced AUTO launch that has FINISHED):
+ * out[0] = that launch's duration in ns, first CTA start to last CTA end on the device's clock;
+ * out[1] = how many launches in a row overran their limit.  Zeros before the first calibration. */
+int gpu_probe_triad_pace_report(uint64_t out[2]);
+
+/* Forget the current device's calibration: VARIANT_AUTO runs the ring until the next
+ * gpu_probe_triad_calibrate(). */
 int gpu_probe_triad_recalibrate(void);
 
 /* Bytes of device scratch the checksum kernels need (a constant). */

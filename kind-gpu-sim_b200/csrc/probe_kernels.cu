@@ -15,7 +15,9 @@
 #include <atomic>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <cuda_runtime.h>
+#include <mutex>
 
 #include "probe_common.cuh"
 #include "probe_launch.h"
@@ -292,6 +294,39 @@ triad_tma(double *__restrict__ a, const double *__restrict__ b, const double *__
   if (LANES) finish_lanes(acc, first, out, ws, red, x);
 }
 
+// How a paced launch reports on itself.  `state` is four words of device memory owned by the
+// device ({earliest CTA start, latest CTA end, ticket, launches in a row that overran}; idle
+// value {~0, 0, 0, n}); the last CTA to finish turns them into a verdict in `report` -- device
+// memory during calibration, pinned host memory the kernel writes over PCIe in steady state, so
+// that the host's NEXT call can look at it with a plain load instead of a synchronisation:
+//   report[0] = nanoseconds from the first CTA's start to the last CTA's end
+//   report[1] = how many launches in a row took longer than limit_ns (limit_ns == 0: untouched)
+// state == nullptr: the launch is not tracked.  Launches that overlap on one device share the
+// four words and measure nonsense (harmless: see auto_triad_pace).
+struct PaceTrack {
+  unsigned long long *state = nullptr;
+  unsigned long long *report = nullptr;
+  unsigned long long limit_ns = 0;
+};
+
+__device__ __forceinline__ void pace_track_finish(const PaceTrack &trk) {  // one thread per CTA
+  atomicMax(&trk.state[1], global_ns());
+  __threadfence();
+  if (atomicAdd(&trk.state[2], 1ull) != gridDim.x - 1) return;
+  __threadfence();
+  const unsigned long long t0 = atomicExch(&trk.state[0], ~0ull);  // read and put back to idle
+  const unsigned long long t1 = atomicExch(&trk.state[1], 0ull);
+  atomicExch(&trk.state[2], 0ull);
+  const unsigned long long ns = t1 - t0;
+  trk.report[0] = ns;
+  if (trk.limit_ns) {
+    const unsigned long long over = ns > trk.limit_ns ? trk.state[3] + 1 : 0;
+    trk.state[3] = over;
+    trk.report[1] = over;
+  }
+  __threadfence_system();
+}
+
 // K1 with PACED refills.  The unpaced ring above is ack-clocked: a slot is refilled the moment
 // it drains, so requests reach the memory system in bursts, and the ring has to be kept small
 // (64 KiB in flight per SM) or mixed read/write traffic over-subscribes HBM and collapses.
@@ -302,16 +337,22 @@ triad_tma(double *__restrict__ a, const double *__restrict__ b, const double *__
 // that cliff is differs from GPU to GPU.  Hence:
 //   * the pace is given in NANOSECONDS and converted with a running estimate of the SM clock
 //     (clock64 against %globaltimer), so a power-capped clock does not change the demand rate;
-//   * the host calibrates the pace per device (calibrate_triad_pace below);
-//   * a one-way ladder guards against drift: over-subscription shows as long consumer stalls
-//     (>= 800 cycles on ~16 % of the tiles instead of 0.3 %); a CTA that sees 5 of them in 64
-//     tiles stops refilling, lets its ring drain and restarts 2 % slower.  It never speeds up.
+//   * the host calibrates the pace per device, in an explicit blocking call
+//     (gpu_probe_triad_calibrate -> calibrate_triad_pace below);
+//   * a one-way ladder guards against drift inside a launch: over-subscription shows as long
+//     consumer stalls (>= 800 cycles on ~16 % of the tiles instead of 0.3 %); a CTA that sees 5
+//     of them in 64 tiles stops refilling, lets its ring drain and restarts 2 % slower.  It
+//     never speeds up;
+//   * every launch also measures itself (PaceTrack: first CTA start to last CTA end on
+//     %globaltimer) and the last CTA leaves the verdict where the HOST can read it without a
+//     synchronisation -- see auto_triad_pace: launches that keep overrunning what their pace
+//     allows send the device back to the unpaced ring.
 // tools/tune/tune_triad.cu (modes hist, ladder, ladderns) holds the experiments.
 template <int TILE, int S, bool LANES>
 __global__ void __launch_bounds__(kThreads)
 triad_tma_paced(double *__restrict__ a, const double *__restrict__ b, const double *__restrict__ c, double s, uint64_t n,
                 uint64_t first, uint64_t *__restrict__ out, uint64_t *__restrict__ ws, const ExchangeArgs x, int pace_ns,
-                unsigned long long *__restrict__ stamps) {
+                const PaceTrack trk) {
   static_assert(TILE % (2 * kThreads) == 0, "tile must split into one f64x2 per thread per pass");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   double *sb = reinterpret_cast<double *>(smem_raw);
@@ -352,7 +393,7 @@ triad_tma_paced(double *__restrict__ a, const double *__restrict__ b, const doub
   if (tid == 0) {
     c_start = clock64();
     g_start = global_ns();
-    if (stamps) atomicMin(&stamps[0], g_start);  // calibration only: when the first CTA started ...
+    if (trk.state) atomicMin(&trk.state[0], g_start);  // when the first CTA started ...
   }
 
   Lanes acc{0, 0};
@@ -417,7 +458,7 @@ triad_tma_paced(double *__restrict__ a, const double *__restrict__ b, const doub
       if (LANES) acc.add(bits(r), 2 * k + 1);
     }
   }
-  if (stamps && tid == 0) atomicMax(&stamps[1], global_ns());  // ... and when the last one finished
+  if (trk.state && tid == 0) pace_track_finish(trk);  // ... and when the last one finished
   if (LANES) finish_lanes(acc, first, out, ws, red, x);
 }
 
@@ -715,91 +756,148 @@ constexpr int kCopyPaceNs = 1426;  // one 32 KiB tile (64 KiB of traffic) per SM
 constexpr int kLdgTriadCtasPerSm = 2;
 constexpr int kLdgChecksumCtasPerSm = 6;
 
-// Per-device pace of the paced triad: 0 = not calibrated yet, < 0 = calibrated, the ring kernel is
-// at least as fast here, > 0 = nanoseconds between refills.  GPU_PROBE_TRIAD_PACE_NS overrides
-// (0 disables the paced kernel, N fixes the pace).
-static std::atomic<int> g_pace_ns[64];
-// A calibration that lands on the slow end of the ladder (or on nothing) may have been taken while
-// something else disturbed the memory system -- eight probes starting at once on one host all
-// landed on 1082 ns and 6700 GB/s, the same GPUs pace at 1016-1040 a moment later.  Such a verdict
-// is tried ONCE more, a few launches later.
-static std::atomic<int> g_pace_attempts[64], g_pace_calls[64];
-constexpr int kPaceSuspectNs = 1052, kPaceRetryAfterCalls = 8;
+// Per-device state of the paced triad.
+//   pace   0 = never calibrated (AUTO uses the unpaced ring), -1 = calibrated: the ring is at least
+//          as fast here, -2 = calibrated, but the drift guard sent the device back to the ring,
+//          > 0 = nanoseconds between a CTA's refills.  GPU_PROBE_TRIAD_PACE_NS overrides all of it
+//          (0 disables the paced kernel, N fixes the pace, untracked).
+//   state  device address of g_pace_state on this device; report: 64 bytes of pinned host memory
+//          the paced kernel's last CTA writes its verdict into (PaceTrack above).
+// Only gpu_probe_triad_calibrate ever blocks; an AUTO launch reads `pace` and one host word.
+struct PaceDevice {
+  std::mutex mu;  // one calibration at a time per device
+  std::atomic<int> pace{0};
+  std::atomic<unsigned long long *> state{nullptr};
+  std::atomic<unsigned long long *> report_host{nullptr}, report_dev{nullptr};
+};
+static PaceDevice g_pace[64];
+static __device__ unsigned long long g_pace_state[4] = {~0ull, 0ull, 0ull, 0ull};
+static __device__ unsigned long long g_pace_cal[16];  // calibration: one duration per candidate pace
+constexpr int kDriftLaunches = 3;                     // launches in a row over the limit before AUTO gives up on pacing
+constexpr int kPaceDemoted = -2;
 
 template <bool LANES>
 static int launch_triad_paced(double *a, const double *b, const double *c, double s, uint64_t n, uint64_t first,
                               uint64_t *out, uint64_t *ws, cudaStream_t st, const ExchangeArgs &x, int pace_ns,
-                              unsigned long long *stamps = nullptr) {
+                              PaceTrack trk = PaceTrack{}, bool with_limit = false) {
   auto k = triad_tma_paced<kPacedTile, kPacedStages, LANES>;
   constexpr size_t smem = TriadTmaSmem<kPacedTile, kPacedStages>::kBytes;
   unsigned grid = 1;
   int rc = persistent_grid(k, smem, n / kPacedTile, &grid, kPacedCtasPerSm);
   if (rc) return rc;
-  k<<<grid, kThreads, smem, st>>>(a, b, c, s, n, first, out, ws, x, pace_ns, stamps);
+  if (with_limit) {
+    // What the pace allows: tiles per CTA x pace.  A launch that behaves lands within 0.5 % of it
+    // (1.8292-1.8337 ms against 1.8252 at 2^29 elements, pace 1030); an over-subscribed one is
+    // 11-25 % off.  4 % + 10 us covers start-up, tail and the first 64 tiles of a 2^26 launch.
+    const uint64_t tiles_per_cta = (n / kPacedTile + grid - 1) / grid;
+    trk.limit_ns = tiles_per_cta * uint64_t(pace_ns) * 104 / 100 + 10000;
+  }
+  k<<<grid, kThreads, smem, st>>>(a, b, c, s, n, first, out, ws, x, pace_ns, trk);
   return launch_rc();
 }
 
-// First AUTO call on a device with a large aligned problem: run the paced kernel at a ladder of
-// paces on the caller's own buffers (the triad is idempotent: whatever these launches write into
-// a[] the real launch writes again) and keep the fastest pace that BEHAVED -- i.e. whose launches
-// took what the pace allows (+5 %) and no more; an over-subscribed launch is 11-25 % off -- one notch
-// slower for margin.  A behaved pace of 1082 ns is 6700 GB/s, what the unpaced ring gives on the
-// slowest GPUs seen, and 1016 ns is 7110 GB/s, above the ring on the fastest; if nothing behaves
-// the ring is used.  Launch durations are taken ON THE DEVICE (first CTA start to last CTA end,
-// %globaltimer), so host-side overhead (a profiler serialising launches) does not change the
-// verdict.  27 launches over at most 2^29 elements and three blocking copies: about 50 ms, once
-// per device per process.
-static __device__ unsigned long long g_pace_stamps[2 * 16];
+// Addresses the tracking needs on device `dev` (current): the device's instance of g_pace_state
+// and a pinned, mapped 64-byte host block.  Called from calibration only (it allocates the block).
+static int pace_resources(int dev) {
+  PaceDevice &pd = g_pace[dev];
+  if (pd.state.load(std::memory_order_acquire) == nullptr) {
+    unsigned long long *p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void **>(&p), g_pace_state);
+    if (e != cudaSuccess) return int(e);
+    pd.state.store(p, std::memory_order_release);
+  }
+  if (pd.report_host.load(std::memory_order_acquire) == nullptr) {
+    void *h = nullptr, *d = nullptr;
+    cudaError_t e = cudaHostAlloc(&h, 64, cudaHostAllocMapped | cudaHostAllocPortable);
+    if (e != cudaSuccess) return int(e);
+    memset(h, 0, 64);
+    e = cudaHostGetDevicePointer(&d, h, 0);
+    if (e != cudaSuccess) { cudaFreeHost(h); return int(e); }
+    pd.report_dev.store(static_cast<unsigned long long *>(d), std::memory_order_release);
+    pd.report_host.store(static_cast<unsigned long long *>(h), std::memory_order_release);
+  }
+  return 0;
+}
 
+// The calibration (gpu_probe_triad_calibrate): run the paced kernel at a ladder of paces on the
+// caller's buffers and keep the fastest pace that BEHAVED -- i.e. whose launches took what the pace
+// allows (+5 %) and no more; an over-subscribed launch is 11-25 % off -- one notch slower for
+// margin.  A behaved pace of 1082 ns is 6700 GB/s, what the unpaced ring gives on the slowest GPUs
+// seen, and 1016 ns is 7110 GB/s, above the ring on the fastest; if nothing behaves the verdict is
+// "ring".  Launch durations are taken ON THE DEVICE (PaceTrack), so host-side overhead (a profiler
+// serialising launches) does not change the verdict.  27 launches over at most 2^29 elements and
+// a few small blocking copies: about 50 ms.
 static int calibrate_triad_pace(double *a, const double *b, const double *c, double s, uint64_t n, cudaStream_t st,
                                 int dev) {
   static const int paces[] = {1004, 1010, 1016, 1023, 1030, 1040, 1052, 1066, 1082};
   constexpr int kN = int(sizeof(paces) / sizeof(paces[0]));
   constexpr int kRuns = 2;  // timed launches per candidate (the slower one counts), after one warm-up launch
-  static_assert(kN <= 16, "stamp slots");
-  const uint64_t m = n < (1ull << 29) ? n : (1ull << 29);
-  unsigned long long *stamps = nullptr;
-  cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void **>(&stamps), g_pace_stamps);
+  static_assert(kN <= 16, "g_pace_cal slots");
+  PaceDevice &pd = g_pace[dev];
+  int rc = pace_resources(dev);
+  if (rc) return rc;
+  unsigned long long *cal = nullptr;
+  cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void **>(&cal), g_pace_cal);
   if (e != cudaSuccess) return int(e);
-  unsigned paced_grid = 1;
-  int rc = persistent_grid(triad_tma_paced<kPacedTile, kPacedStages, false>, TriadTmaSmem<kPacedTile, kPacedStages>::kBytes,
-                           m / kPacedTile, &paced_grid, kPacedCtasPerSm);
-  if (rc) return rc;
-  const double tiles_per_cta = double((m / kPacedTile + paced_grid - 1) / paced_grid);
-  unsigned long long host[2 * 16];
-  double worst_ms[kN];
-  for (int i = 0; i < kN; ++i) worst_ms[i] = 0;
-  for (int run = -1; run < kRuns && rc == 0; ++run) {  // run -1 warms up (and is measured, but not used)
-    for (int i = 0; i < 2 * kN; ++i) host[i] = (i & 1) ? 0ull : ~0ull;  // {min start, max end} per candidate
-    if (cudaMemcpyAsync(stamps, host, sizeof(unsigned long long) * 2 * kN, cudaMemcpyHostToDevice, st) != cudaSuccess)
-      return int(cudaGetLastError());
-    for (int i = 0; i < kN && rc == 0; ++i)
-      rc = launch_triad_paced<false>(a, b, c, s, m, 0, nullptr, nullptr, st, ExchangeArgs{}, paces[i], stamps + 2 * i);
-    if (rc) break;
-    if (cudaMemcpyAsync(host, stamps, sizeof(unsigned long long) * 2 * kN, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
-        cudaStreamSynchronize(st) != cudaSuccess)
-      return int(cudaGetLastError());
-    if (run < 0) continue;
-    for (int i = 0; i < kN; ++i) {
-      const double ms = double(host[2 * i + 1] - host[2 * i]) * 1e-6;
-      if (ms > worst_ms[i]) worst_ms[i] = ms;
-    }
-  }
-  if (rc) return rc;
-  int best = -1;
-  for (int i = 0; i < kN; ++i) {
-    const double ideal_ms = tiles_per_cta * paces[i] * 1e-6;
-    // 5 %: start-up, tail and the first 64 tiles (paced for an assumed 2 GHz clock) cost 1-2 % of a launch this short
-    if (worst_ms[i] > 0 && worst_ms[i] <= ideal_ms * 1.05 && (best < 0 || worst_ms[i] < worst_ms[best])) best = i;
-  }
+  static const int forced_verdict = [] { const char *v = getenv("GPU_PROBE_TRIAD_FORCE_VERDICT_NS"); return v ? atoi(v) : 0; }();
+  const unsigned long long idle[4] = {~0ull, 0ull, 0ull, 0ull};
+  unsigned long long *state = pd.state.load(std::memory_order_acquire);
   int chosen = -1;
-  if (best >= 0) chosen = paces[best + 1 < kN ? best + 1 : best];  // one notch (~0.7 %) slower than the fastest that behaved
-  g_pace_ns[dev].store(chosen, std::memory_order_release);
+  if (forced_verdict != 0) {  // tests: pretend the ladder came out at this pace (< 0: "ring")
+    chosen = forced_verdict;
+  } else {
+    const uint64_t m = n < (1ull << 29) ? n : (1ull << 29);
+    unsigned paced_grid = 1;
+    rc = persistent_grid(triad_tma_paced<kPacedTile, kPacedStages, false>, TriadTmaSmem<kPacedTile, kPacedStages>::kBytes,
+                         m / kPacedTile, &paced_grid, kPacedCtasPerSm);
+    if (rc) return rc;
+    const double tiles_per_cta = double((m / kPacedTile + paced_grid - 1) / paced_grid);
+    unsigned long long host[16];
+    double worst_ms[kN];
+    for (int i = 0; i < kN; ++i) worst_ms[i] = 0;
+    if (cudaMemcpyAsync(state, idle, sizeof idle, cudaMemcpyHostToDevice, st) != cudaSuccess) return int(cudaGetLastError());
+    for (int run = -1; run < kRuns; ++run) {  // run -1 warms up (and is measured, but not used)
+      for (int i = 0; i < kN; ++i) {
+        PaceTrack trk;
+        trk.state = state;
+        trk.report = cal + i;
+        if ((rc = launch_triad_paced<false>(a, b, c, s, m, 0, nullptr, nullptr, st, ExchangeArgs{}, paces[i], trk))) return rc;
+      }
+      if (cudaMemcpyAsync(host, cal, sizeof(unsigned long long) * kN, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+          cudaStreamSynchronize(st) != cudaSuccess)
+        return int(cudaGetLastError());
+      if (run < 0) continue;
+      for (int i = 0; i < kN; ++i) {
+        const double ms = double(host[i]) * 1e-6;
+        if (ms > worst_ms[i]) worst_ms[i] = ms;
+      }
+    }
+    int best = -1;
+    for (int i = 0; i < kN; ++i) {
+      const double ideal_ms = tiles_per_cta * paces[i] * 1e-6;
+      // 5 %: start-up, tail and the first 64 tiles (paced for an assumed 2 GHz clock) cost 1-2 % of a launch this short
+      if (worst_ms[i] > 0 && worst_ms[i] <= ideal_ms * 1.05 && (best < 0 || worst_ms[i] < worst_ms[best])) best = i;
+    }
+    if (best >= 0) chosen = paces[best + 1 < kN ? best + 1 : best];  // one notch (~0.7 %) slower than the fastest that behaved
+  }
+  // a fresh verdict starts with a clean record: no overruns counted on the device or seen by the host
+  if (cudaMemcpyAsync(state, idle, sizeof idle, cudaMemcpyHostToDevice, st) != cudaSuccess ||
+      cudaStreamSynchronize(st) != cudaSuccess)
+    return int(cudaGetLastError());
+  volatile unsigned long long *rep = pd.report_host.load(std::memory_order_acquire);
+  rep[0] = rep[1] = 0;
+  pd.pace.store(chosen, std::memory_order_release);
   return 0;
 }
 
-// Pace for an AUTO call on the current device (calibrating if this is the first one), or <= 0 for "use the ring".
-static int auto_triad_pace(double *a, const double *b, const double *c, double s, uint64_t n, cudaStream_t st, int *pace) {
+// Pace for an AUTO call on the current device, or <= 0 for "use the ring"; fills `trk` when the
+// launch is to report on itself.  Never blocks, never calibrates: a device nobody calibrated runs
+// the ring.  The drift guard: the previous paced launches left their verdict in pinned host memory
+// (PaceTrack); kDriftLaunches launches in a row that overran what the pace allows -- the memory
+// system sustains less than when the device was calibrated -- and the device goes back to the ring
+// until somebody calibrates again.  The host reads one word; what it sees may lag the GPU by the
+// launches still in flight, which only delays the verdict.
+static int auto_triad_pace(int *pace, PaceTrack *trk) {
   static const int forced = [] { const char *e = getenv("GPU_PROBE_TRIAD_PACE_NS"); return e ? atoi(e) : -1; }();
   *pace = -1;
   if (forced >= 0) { *pace = forced; return 0; }
@@ -807,24 +905,18 @@ static int auto_triad_pace(double *a, const double *b, const double *c, double s
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return int(e);
   if (dev < 0 || dev >= 64) return 0;
-  int p = g_pace_ns[dev].load(std::memory_order_acquire);
-  if (p != 0 && (p < 0 || p > kPaceSuspectNs) && g_pace_attempts[dev].load(std::memory_order_relaxed) < 2 &&
-      g_pace_calls[dev].fetch_add(1, std::memory_order_relaxed) + 1 >= kPaceRetryAfterCalls)
-    p = 0;  // suspiciously slow first verdict: calibrate once more
-  if (p == 0) {
-    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-    if (cudaStreamIsCapturing(st, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) {
-      cudaGetLastError();
-      return 0;  // never calibrate (and synchronise) inside a capture: ring kernel, calibrate another time
+  PaceDevice &pd = g_pace[dev];
+  int p = pd.pace.load(std::memory_order_acquire);
+  if (p > 0) {
+    volatile unsigned long long *rep = pd.report_host.load(std::memory_order_acquire);
+    if (rep && rep[1] >= kDriftLaunches) {
+      int expect = p;
+      pd.pace.compare_exchange_strong(expect, kPaceDemoted, std::memory_order_acq_rel);
+      p = kPaceDemoted;
+    } else if (rep) {
+      trk->state = pd.state.load(std::memory_order_acquire);
+      trk->report = pd.report_dev.load(std::memory_order_acquire);
     }
-    int rc = calibrate_triad_pace(a, b, c, s, n, st, dev);
-    if (rc) {  // calibration is an optimisation: if it cannot run, the unpaced ring can
-      cudaGetLastError();
-      g_pace_ns[dev].store(-1, std::memory_order_release);
-    }
-    g_pace_attempts[dev].fetch_add(1, std::memory_order_relaxed);
-    g_pace_calls[dev].store(0, std::memory_order_relaxed);
-    p = g_pace_ns[dev].load(std::memory_order_acquire);
   }
   *pace = p;
   return 0;
@@ -841,8 +933,9 @@ static int launch_triad(double *a, const double *b, const double *c, double s, u
     variant = g_auto_triad;
     if (al16 && n >= kPacedMinElems) {
       int pace = -1;
-      if ((rc = auto_triad_pace(a, b, c, s, n, st, &pace))) return rc;
-      if (pace > 0) return launch_triad_paced<LANES>(a, b, c, s, n, first, out, ws, st, x, pace);
+      PaceTrack trk;
+      if ((rc = auto_triad_pace(&pace, &trk))) return rc;
+      if (pace > 0) return launch_triad_paced<LANES>(a, b, c, s, n, first, out, ws, st, x, pace, trk, trk.state != nullptr);
     }
   }
   if (!al16) {
@@ -853,7 +946,7 @@ static int launch_triad(double *a, const double *b, const double *c, double s, u
   }
   if (variant == GPU_PROBE_VARIANT_TMA_PACED) {
     int dev = 0, pace = 0;
-    if (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < 64) pace = g_pace_ns[dev].load(std::memory_order_acquire);
+    if (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < 64) pace = g_pace[dev].pace.load(std::memory_order_acquire);
     return launch_triad_paced<LANES>(a, b, c, s, n, first, out, ws, st, x, pace > 0 ? pace : kPacedDefaultNs);
   }
   if (variant == GPU_PROBE_VARIANT_TMA) {
@@ -1014,21 +1107,58 @@ int gpu_probe_triad(double *a, const double *b, const double *c, double s, uint6
                              ExchangeArgs{});
 }
 
+int gpu_probe_triad_calibrate(double *a, const double *b, const double *c, uint64_t n, void *stream) {
+  if (!a || !b || !c) return GPU_PROBE_EINVAL;
+  if (!aligned(a, 8) || !aligned(b, 8) || !aligned(c, 8)) return GPU_PROBE_EALIGN;
+  // the launches below overwrite a[] many times while reading b[] and c[]: in place is not possible
+  const uintptr_t pa = reinterpret_cast<uintptr_t>(a), pb = reinterpret_cast<uintptr_t>(b), pc = reinterpret_cast<uintptr_t>(c);
+  const uintptr_t len = uintptr_t(n) * sizeof(double);
+  if ((pa < pb + len && pb < pa + len) || (pa < pc + len && pc < pa + len)) return GPU_PROBE_EINVAL;
+  if (n < kPacedMinElems || !aligned(a, 16) || !aligned(b, 16) || !aligned(c, 16)) return 0;  // AUTO never paces such a call
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  cudaError_t e = cudaStreamIsCapturing(st, &cap);
+  if (e != cudaSuccess) return int(e);
+  if (cap != cudaStreamCaptureStatusNone) return int(cudaErrorStreamCaptureUnsupported);
+  int dev = 0;
+  if ((e = cudaGetDevice(&dev)) != cudaSuccess) return int(e);
+  if (dev < 0 || dev >= 64) return 0;  // beyond the table: such a device simply runs the ring
+  std::lock_guard<std::mutex> lock(g_pace[dev].mu);
+  int rc = calibrate_triad_pace(a, b, c, GPU_PROBE_SCALAR, n, st, dev);
+  if (rc) {  // pacing is an optimisation: a device that cannot be calibrated runs the ring
+    cudaGetLastError();
+    g_pace[dev].pace.store(0, std::memory_order_release);
+  }
+  return rc;
+}
+
 int gpu_probe_triad_pace_ns(void) {
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
-  return g_pace_ns[dev].load(std::memory_order_acquire);
+  PaceDevice &pd = g_pace[dev];
+  int p = pd.pace.load(std::memory_order_acquire);
+  volatile unsigned long long *rep = pd.report_host.load(std::memory_order_acquire);
+  if (p > 0 && rep && rep[1] >= kDriftLaunches) p = kPaceDemoted;  // what the next AUTO launch will decide
+  return p;
+}
+
+int gpu_probe_triad_pace_report(uint64_t out[2]) {
+  if (!out) return GPU_PROBE_EINVAL;
+  out[0] = out[1] = 0;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return int(e);
+  if (dev < 0 || dev >= 64) return 0;
+  volatile unsigned long long *rep = g_pace[dev].report_host.load(std::memory_order_acquire);
+  if (rep) { out[0] = rep[0]; out[1] = rep[1]; }
+  return 0;
 }
 
 int gpu_probe_triad_recalibrate(void) {
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return int(e);
-  if (dev >= 0 && dev < 64) {
-    g_pace_ns[dev].store(0, std::memory_order_release);
-    g_pace_attempts[dev].store(0, std::memory_order_relaxed);
-    g_pace_calls[dev].store(0, std::memory_order_relaxed);
-  }
+  if (dev >= 0 && dev < 64) g_pace[dev].pace.store(0, std::memory_order_release);
   return 0;
 }
 

@@ -55,6 +55,8 @@ def lib() -> ctypes.CDLL:
         L.gpu_probe_error_string.argtypes = [ctypes.c_int]
         L.gpu_probe_init_fill.argtypes = [_vp, _u64, _u64, _u64, _vp]
         L.gpu_probe_triad.argtypes = [_vp, _vp, _vp, ctypes.c_double, _u64, ctypes.c_int, _vp]
+        L.gpu_probe_triad_calibrate.argtypes = [_vp, _vp, _vp, _u64, _vp]
+        L.gpu_probe_triad_calibrate.restype = ctypes.c_int
         L.gpu_probe_checksum_workspace_bytes.restype = ctypes.c_size_t
         L.gpu_probe_checksum_u64.argtypes = [_vp, _u64, _u64, _vp, _vp, ctypes.c_int, _vp]
         L.gpu_probe_checksum_u64_noalloc.argtypes = [_vp, _u64, _u64, _vp, _vp]
@@ -112,10 +114,25 @@ def kernel_info() -> str:
 
 
 def triad_pace_ns() -> int:
-    """AUTO's calibrated pace on the current device (0: not yet, < 0: unpaced ring, > 0: ns per refill)."""
+    """AUTO's pacing on the current device: 0 never calibrated, -1 ring is as fast, -2 demoted by the drift guard, > 0 ns per refill."""
     L = lib()
     L.gpu_probe_triad_pace_ns.restype = ctypes.c_int
     return int(L.gpu_probe_triad_pace_ns())
+
+
+def triad_calibrate(a: int, b: int, c: int, n: int, stream: int = 0) -> int:
+    """[blocking] Calibrate AUTO's paced triad for the current device on the caller's buffers; returns the verdict."""
+    _check(lib().gpu_probe_triad_calibrate(a, b, c, n, stream), "gpu_probe_triad_calibrate")
+    return triad_pace_ns()
+
+
+def triad_pace_report() -> "tuple[int, int]":
+    """(duration in ns of the last finished paced AUTO launch, overruns in a row) on the current device."""
+    out = (_u64 * 2)()
+    L = lib()
+    L.gpu_probe_triad_pace_report.restype = ctypes.c_int
+    _check(L.gpu_probe_triad_pace_report(out), "gpu_probe_triad_pace_report")
+    return int(out[0]), int(out[1])
 
 
 def triad_recalibrate() -> None:

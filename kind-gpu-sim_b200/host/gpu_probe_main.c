@@ -64,6 +64,7 @@ typedef struct {
   int max_gpus;            /* use at most this many of the visible GPUs (0: all) */
   int allreduce_algo;      /* GPU_PROBE_ALLREDUCE_* for the probe's own allreduce */
   const char *allreduce_algo_name;
+  int inject_fault;        /* flip one bit of a[] between K1 and K2: the run must end in rc 6 */
 } options;
 
 static int g_status = RC_OK; /* first failure wins */
@@ -85,7 +86,9 @@ static void die_usage(const char *fmt, ...) {
           "\nusage: gpu-probe [--expect-gpus=N] [--bytes=B] [--iters=K] [--warmup=W]\n"
           "                 [--variant=auto|ldg128|tma|ldg256] [--max-gpus=N]\n"
           "                 [--sweep-max-bytes=B] [--p2p-bytes=B] [--no-sweep] [--no-p2p] [--no-sharded]\n"
-          "                 [--measured-hbm-gbs=X] [--allreduce-algo=auto|pull_push|push|multimem]\n");
+          "                 [--measured-hbm-gbs=X] [--allreduce-algo=auto|pull_push|push|multimem]\n"
+          "                 [--inject-fault]\n"
+          "environment: GPU_PROBE_MEASURED_HBM_GBS=X (as the flag; the flag wins)\n");
   printf("PROBE FAIL rc=%d\n", RC_USAGE);
   exit(RC_USAGE);
 }
@@ -120,6 +123,11 @@ static void parse_options(int argc, char **argv, options *o) {
   o->max_gpus = 0;
   o->allreduce_algo = GPU_PROBE_ALLREDUCE_AUTO;
   o->allreduce_algo_name = "auto";
+  o->inject_fault = 0;
+  { /* the pod runner / operator exports what this box's HBM was measured to sustain */
+    const char *m = getenv("GPU_PROBE_MEASURED_HBM_GBS");
+    if (m && *m) o->measured_hbm_gbs = atof(m);
+  }
   for (int i = 1; i < argc; ++i) {
     const char *a = argv[i], *v;
     if ((v = flag_value(a, "--expect-gpus"))) o->expect_gpus = (int)parse_u64("--expect-gpus", v);
@@ -147,6 +155,7 @@ static void parse_options(int argc, char **argv, options *o) {
     } else if (!strcmp(a, "--no-sweep")) o->do_sweep = 0;
     else if (!strcmp(a, "--no-p2p")) o->do_p2p = 0;
     else if (!strcmp(a, "--no-sharded")) o->do_sharded = 0;
+    else if (!strcmp(a, "--inject-fault")) o->inject_fault = 1;
     else if (!strcmp(a, "--help") || !strcmp(a, "-h")) die_usage("help");
     else die_usage("unknown argument '%s'", a);
   }
@@ -205,6 +214,8 @@ static int nccl_load(nccl_api *n) {
     *(void **)(&n->field) = dlsym(n->so, name);                              \
     if (!n->field) {                                                         \
       fprintf(stderr, "gpu-probe: NCCL symbol %s missing\n", name);          \
+      dlclose(n->so);                                                        \
+      memset(n, 0, sizeof(*n)); /* so == NULL: every phase skips NCCL */     \
       return RC_NCCL;                                                        \
     }                                                                        \
   } while (0)
@@ -327,6 +338,16 @@ static int phase_hbm(const options *o, gpu_state *gs, int ng, uint64_t n) {
   }
   int rc = sync_all(gs, ng);
   if (rc) return rc;
+  /* AUTO's paced triad: the one blocking step, made here, one GPU at a time (a device calibrated
+   * while its neighbours stream lands on a slower pace), before anything is timed */
+  if (o->variant == GPU_PROBE_VARIANT_AUTO)
+    for (int d = 0; d < ng; ++d) {
+      CU(cudaSetDevice(gs[d].dev));
+      const double t0 = now_s();
+      PR(gpu_probe_triad_calibrate(gs[d].a, gs[d].b, gs[d].c, n, gs[d].st));
+      printf("PROBE INFO triad_calibrate gpu=%d pace_ns=%d ms=%.1f\n", gs[d].dev, gpu_probe_triad_pace_ns(),
+             (now_s() - t0) * 1e3);
+    }
 
   for (int k = 0; k < K_COUNT; ++k) {
     /* every GPU runs the same kernel at the same time (config 4: 8 concurrent probes) */
@@ -340,6 +361,16 @@ static int phase_hbm(const options *o, gpu_state *gs, int ng, uint64_t n) {
       }
     }
     if ((rc = sync_all(gs, ng))) return rc;
+    if (k == K_TRIAD && o->inject_fault) /* the checksum that follows must notice: match=0, exit 6 */
+      for (int d = 0; d < ng; ++d) {
+        uint64_t w = 0;
+        const uint64_t at = n / 2;
+        CU(cudaSetDevice(gs[d].dev));
+        CU(cudaMemcpy(&w, gs[d].a + at, 8, cudaMemcpyDeviceToHost));
+        w ^= 1ull << 17;
+        CU(cudaMemcpy(gs[d].a + at, &w, 8, cudaMemcpyHostToDevice));
+        printf("PROBE INFO inject_fault gpu=%d element=%" PRIu64 " bit=17\n", gs[d].dev, at);
+      }
     double sum_gbs = 0, worst_ms = 0;
     const uint64_t bytes = k_bytes_per_elem[k] * n;
     for (int d = 0; d < ng; ++d) {

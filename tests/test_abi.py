@@ -52,6 +52,11 @@ def test_argument_validation_needs_no_gpu():
     assert L.gpu_probe_triad(None, None, None, 3.0, 4, 0, None) == gpuprobe.EINVAL
     assert L.gpu_probe_triad(0x1000, 0x2000, 0x3000, 3.0, 4, 7, None) == gpuprobe.EINVAL   # unknown variant
     assert L.gpu_probe_triad(0x1000, 0x2004, 0x3000, 3.0, 4, 0, None) == gpuprobe.EALIGN
+    assert L.gpu_probe_triad_calibrate(None, 0x2000, 0x3000, 1 << 26, None) == gpuprobe.EINVAL
+    assert L.gpu_probe_triad_calibrate(0x1004, 0x2000, 0x3000, 4, None) == gpuprobe.EALIGN
+    assert L.gpu_probe_triad_calibrate(0x1000, 0x1000, 0x3000, 4, None) == gpuprobe.EINVAL   # a aliases b
+    assert L.gpu_probe_triad_calibrate(0x1000, 0x2000, 0x1010, 4, None) == gpuprobe.EINVAL   # a overlaps c
+    assert L.gpu_probe_triad_calibrate(0x1000, 0x2000, 0x3000, 4, None) == 0                 # too small to pace: no-op
     assert L.gpu_probe_checksum_u64(0x1000, 4, 0, None, None, 0, None) == gpuprobe.EINVAL
     assert L.gpu_probe_checksum_u64(0x1000, 4, 0, 0x2000, 0x3000, -2, None) == gpuprobe.EINVAL
     assert L.gpu_probe_triad_checksum(None, None, None, 3.0, 4, 0, 0x2000, 0x3000, 0, None) == gpuprobe.EINVAL

@@ -1,0 +1,79 @@
+"""AUTO's pacing never blocks the caller's steady state.
+
+Round 1 hid a second 55 ms calibration (27 launches and a stream synchronise) behind the eighth
+AUTO call whenever the first verdict looked slow; with `--warmup 5 --steps 20` that landed inside
+the timed loop and halved the 4- and 8-GPU figures.  Now only gpu_probe_triad_calibrate blocks.
+Each case runs in its own process because the verdict is forced through an environment variable
+the library reads once (GPU_PROBE_TRIAD_FORCE_VERDICT_NS: the ladder "came out" at this pace)."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+SNIPPET = r'''
+import json, os, sys, time
+sys.path.insert(0, os.path.join(%(root)r, "kind-gpu-sim_b200"))
+import numpy as np, torch, gpuprobe
+n = 1 << 27
+st = torch.cuda.current_stream().cuda_stream
+b = torch.empty(n, dtype=torch.float64, device="cuda"); c = torch.empty_like(b); a = torch.empty_like(b)
+ws = torch.zeros(gpuprobe.workspace_bytes() // 8, dtype=torch.int64, device="cuda")
+out = torch.zeros(2, dtype=torch.int64, device="cuda")
+gpuprobe.init_fill(b.data_ptr(), n, 0, gpuprobe.SEED_B, st)
+gpuprobe.init_fill(c.data_ptr(), n, 0, gpuprobe.SEED_C, st)
+torch.cuda.synchronize()
+verdict = gpuprobe.triad_calibrate(a.data_ptr(), b.data_ptr(), c.data_ptr(), n, st)
+host_ms, paces = [], []
+for k in range(50):
+    t0 = time.perf_counter()
+    gpuprobe.triad(a.data_ptr(), b.data_ptr(), c.data_ptr(), gpuprobe.SCALAR, n, gpuprobe.VARIANT_AUTO, st)
+    host_ms.append((time.perf_counter() - t0) * 1e3)
+    if k %% 10 == 9:
+        torch.cuda.synchronize()   # lets the verdicts of the launches so far reach the host
+        paces.append(gpuprobe.triad_pace_ns())
+gpuprobe.checksum_u64(a.data_ptr(), n, 0, out.data_ptr(), ws.data_ptr(), gpuprobe.VARIANT_LDG, st)
+torch.cuda.synchronize()
+print(json.dumps({"verdict": verdict, "host_ms_max": max(host_ms), "paces": paces,
+                  "lanes": [int(v) for v in out.cpu().numpy().view(np.uint64)]}))
+'''
+
+
+def run_case(forced_verdict_ns):
+    env = dict(os.environ, GPU_PROBE_TRIAD_FORCE_VERDICT_NS=str(forced_verdict_ns))
+    env.pop("GPU_PROBE_TRIAD_PACE_NS", None)
+    r = subprocess.run([sys.executable, "-c", SNIPPET % {"root": ROOT}], capture_output=True, text=True, env=env,
+                       timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    return json.loads(r.stdout.strip().splitlines()[-1])
+
+
+def test_a_slow_verdict_is_never_retried_behind_the_callers_back(golden):
+    """1082 ns is the slow end of the ladder -- the verdict round 1 re-examined on the 8th call."""
+    got = run_case(1082)
+    assert got["verdict"] == 1082
+    assert got["host_ms_max"] < 1.0, got      # 50 AUTO calls, each a bare asynchronous launch
+    assert got["paces"] == [1082] * 5, got    # behaved launches: the verdict stands, nothing re-calibrated
+    assert got["lanes"] == [int(v, 16) for v in golden["pow2_lanes"][27]]
+
+
+def test_a_ring_verdict_keeps_auto_on_the_ring(golden):
+    got = run_case(-1)
+    assert got["verdict"] == -1 and got["paces"] == [-1] * 5 and got["host_ms_max"] < 1.0, got
+    assert got["lanes"] == [int(v, 16) for v in golden["pow2_lanes"][27]]
+
+
+def test_drift_guard_sends_an_overrunning_device_back_to_the_ring(golden):
+    """A pace HBM cannot sustain (900 ns asks for 8 TB/s): every launch overruns what the pace
+    allows, the kernel's last CTA says so in pinned host memory, and after three such launches the
+    next AUTO call -- still without blocking -- uses the ring.  The bits never change."""
+    got = run_case(900)
+    assert got["verdict"] == 900
+    assert got["host_ms_max"] < 1.0, got
+    assert got["paces"] == [-2] * 5, got
+    assert got["lanes"] == [int(v, 16) for v in golden["pow2_lanes"][27]]

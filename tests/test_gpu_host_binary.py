@@ -50,6 +50,38 @@ def test_size_without_known_answer_reports_na_but_still_cross_checks():
     assert res[3]["lanes"] == res[2]["lanes"]
 
 
+def test_injected_fault_is_caught_and_exits_6():
+    """--inject-fault flips bit 17 of a[n/2] between K1 and K2: the checksum must disagree with the
+    known answer (match=0) and with the fused kernel's lanes, and the pod must fail with rc 6."""
+    log2n = 24
+    r, res = run("--max-gpus=1", f"--bytes={8 << log2n}", "--iters=2", "--warmup=1", "--inject-fault")
+    assert r.returncode == 6, r.stdout + r.stderr
+    assert "PROBE FAIL rc=6" in r.stdout and "PROBE INFO inject_fault gpu=0" in r.stdout
+    want = oracle.stream_lanes(1 << log2n, 0)
+    by = {x["kind"]: x for x in res}
+    assert by["checksum"]["match"] == "0" and by["checksum"]["lanes"] != f"{want[0]:016x},{want[1]:016x}"
+    # exactly the flipped bit: lane0 differs by +-2^17, nothing else
+    got0 = int(by["checksum"]["lanes"].split(",")[0], 16)
+    assert (got0 - want[0]) % (1 << 64) in (1 << 17, (1 << 64) - (1 << 17))
+    assert by["triad_checksum"]["match"] == "1"  # the fused pass recomputes a[] and is clean again
+    # and on a size without a known answer the fused-vs-separate cross-check still catches it
+    r, res = run("--max-gpus=1", f"--bytes={8 * ((1 << 20) + 8)}", "--iters=2", "--warmup=1", "--inject-fault")
+    assert r.returncode == 6 and "fused lanes differ" in r.stderr
+
+
+def test_calibration_is_reported_before_anything_is_timed():
+    r, _ = run("--max-gpus=1", "--bytes=1g", "--iters=3", "--warmup=1")
+    assert r.returncode == 0, r.stdout + r.stderr
+    lines = r.stdout.splitlines()
+    cal = [i for i, ln in enumerate(lines) if ln.startswith("PROBE INFO triad_calibrate gpu=0 pace_ns=")]
+    first_result = min(i for i, ln in enumerate(lines) if ln.startswith("RESULT "))
+    assert len(cal) == 1 and cal[0] < first_result
+    pace = int(re.search(r"pace_ns=(-?\d+)", lines[cal[0]]).group(1))
+    assert pace == -1 or 1000 <= pace <= 1100
+    triad = [ln for ln in lines if ln.startswith("RESULT kind=triad ")][0]
+    assert f"pace_ns={pace}" in triad  # the verdict stood through the timed launches
+
+
 def test_device_count_contract():
     have = torch.cuda.device_count()
     r, _ = run(f"--expect-gpus={have + 1}", "--bytes=1m")

@@ -261,19 +261,56 @@ def test_beyond_2_32_elements_matches_golden(golden):
     torch.cuda.empty_cache()
 
 
-def test_auto_triad_calibrates_once_and_stays_bit_exact(golden):
-    """AUTO at >= 2^26 elements calibrates a per-device pace on first use (timed launches on the
-    caller's buffers) and then runs the paced kernel: whatever pace it picks, the bits are the same."""
+def test_auto_triad_is_bit_exact_before_and_after_an_explicit_calibration(golden):
+    """AUTO never calibrates by itself: an uncalibrated device runs the ring (pace 0).  After
+    gpu_probe_triad_calibrate on the caller's buffers AUTO at >= 2^26 elements may run the paced
+    kernel: whatever the verdict, the bits are the same."""
     n = 1 << 27
     want = tuple(int(v, 16) for v in golden["pow2_lanes"][27])
     b, c, a = gpu_init(n, 0, oracle.SEED_B), gpu_init(n, 0, oracle.SEED_C), f64(n)
     ws = workspace()
-    for rep in range(3):
+    gpuprobe.triad_recalibrate()
+    assert gpuprobe.triad_pace_ns() == 0
+    a.fill_(-1.0)
+    gpuprobe.triad(a.data_ptr(), b.data_ptr(), c.data_ptr(), gpuprobe.SCALAR, n, gpuprobe.VARIANT_AUTO, stream())
+    assert gpu_checksum(a, 0, gpuprobe.VARIANT_AUTO, ws) == want
+    assert gpuprobe.triad_pace_ns() == 0  # launching did not calibrate
+    verdict = gpuprobe.triad_calibrate(a.data_ptr(), b.data_ptr(), c.data_ptr(), n, stream())
+    assert verdict == -1 or 1000 <= verdict <= 1100, verdict
+    for rep in range(4):  # the probe's own step: triad, then the checksum of what it wrote
+        gpuprobe.triad(a.data_ptr(), b.data_ptr(), c.data_ptr(), gpuprobe.SCALAR, n, gpuprobe.VARIANT_AUTO, stream())
+        assert gpu_checksum(a, 0, gpuprobe.VARIANT_AUTO, ws) == want, rep
+    assert gpuprobe.triad_pace_ns() == verdict  # behaved launches do not trip the drift guard
+    if verdict > 0:
+        ns, over = gpuprobe.triad_pace_report()
+        ideal = -(-(n // 1024) // (2 * torch.cuda.get_device_properties(0).multi_processor_count)) * verdict
+        assert over == 0 and 0.98 * ideal <= ns <= 1.04 * ideal + 10000, (ns, ideal)
+    for rep in range(4):
+        # a[] refilled right before: the triad starts into an L2 full of dirty lines, runs 15-22 % over what
+        # its pace allows (tools/pace_guard_probe.py) and the guard may send AUTO back to the ring -- same bits
         a.fill_(-1.0)
         gpuprobe.triad(a.data_ptr(), b.data_ptr(), c.data_ptr(), gpuprobe.SCALAR, n, gpuprobe.VARIANT_AUTO, stream())
         assert gpu_checksum(a, 0, gpuprobe.VARIANT_AUTO, ws) == want, rep
+    assert gpuprobe.triad_pace_ns() in (verdict, -2)
     out = lanes_buf()
     gpuprobe.triad_checksum(a.data_ptr(), b.data_ptr(), c.data_ptr(), gpuprobe.SCALAR, n, 0, out.data_ptr(), ws.data_ptr(),
                             gpuprobe.VARIANT_TMA_PACED, stream())
     torch.cuda.synchronize()
     assert lanes_of(out) == want
+    gpuprobe.triad_recalibrate()
+
+
+def test_calibrate_rejects_overlapping_buffers_and_ignores_small_problems():
+    n = 1 << 26
+    buf = f64(2 * n)
+    L = gpuprobe.lib()
+    gpuprobe.triad_recalibrate()
+    # a[] aliases b[] (in place) or overlaps c[] by one element: the launches could not be replayed
+    assert L.gpu_probe_triad_calibrate(buf.data_ptr(), buf.data_ptr(), buf.data_ptr() + 8 * n, n, stream()) == gpuprobe.EINVAL
+    assert L.gpu_probe_triad_calibrate(buf.data_ptr() + 8 * (n - 1), buf.data_ptr() + 8 * n, buf.data_ptr(), n - 2, stream()) == gpuprobe.EINVAL
+    # below 2^26 elements, or 8-byte-aligned only: nothing to calibrate, nothing changes
+    small = f64(3 * 1024)
+    assert L.gpu_probe_triad_calibrate(small.data_ptr(), small.data_ptr() + 8192, small.data_ptr() + 16384, 1024, stream()) == 0
+    assert gpuprobe.triad_pace_ns() == 0
+    del buf
+    torch.cuda.empty_cache()

@@ -28,6 +28,7 @@ def test_usage_errors_exit_2():
         r = subprocess.run([BIN, *bad], capture_output=True, text=True)
         assert r.returncode == 2, (bad, r.stdout, r.stderr)
         assert "PROBE FAIL rc=2" in r.stdout and "usage:" in r.stderr
+    assert "--inject-fault" in r.stderr and "GPU_PROBE_MEASURED_HBM_GBS" in r.stderr
 
 
 @pytest.mark.skipif(not _no_gpu(), reason="only meaningful on a machine without a GPU")

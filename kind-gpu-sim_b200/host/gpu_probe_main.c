@@ -198,6 +198,13 @@ typedef struct {
   ncclResult_t (*GroupStart)(void);
   ncclResult_t (*GroupEnd)(void);
   const char *(*GetErrorString)(ncclResult_t);
+  /* optional (NCCL >= 2.19 / 2.27): user-buffer registration, what SURVEY 8(d) specifies for the sweep */
+  ncclResult_t (*MemAlloc)(void **, size_t);
+  ncclResult_t (*MemFree)(void *);
+  ncclResult_t (*CommRegister)(const ncclComm_t, void *, size_t, void **);
+  ncclResult_t (*CommDeregister)(const ncclComm_t, void *);
+  ncclResult_t (*CommWindowRegister)(ncclComm_t, void *, size_t, ncclWindow_t *, int);
+  ncclResult_t (*CommWindowDeregister)(ncclComm_t, ncclWindow_t);
 } nccl_api;
 
 static int nccl_load(nccl_api *n) {
@@ -227,6 +234,12 @@ static int nccl_load(nccl_api *n) {
   SYM(GroupEnd, "ncclGroupEnd");
   SYM(GetErrorString, "ncclGetErrorString");
 #undef SYM
+  *(void **)(&n->MemAlloc) = dlsym(n->so, "ncclMemAlloc");
+  *(void **)(&n->MemFree) = dlsym(n->so, "ncclMemFree");
+  *(void **)(&n->CommRegister) = dlsym(n->so, "ncclCommRegister");
+  *(void **)(&n->CommDeregister) = dlsym(n->so, "ncclCommDeregister");
+  *(void **)(&n->CommWindowRegister) = dlsym(n->so, "ncclCommWindowRegister");
+  *(void **)(&n->CommWindowDeregister) = dlsym(n->so, "ncclCommWindowDeregister");
   return 0;
 }
 
@@ -567,8 +580,8 @@ static int time_allreduce(const options *o, int use_nccl, nccl_api *nc, ncclComm
 }
 
 /* Integer-valued floats in, closed-form sum out: exact in fp32 whatever the reduction order. */
-static int check_allreduce(const options *o, int use_nccl, nccl_api *nc, ncclComm_t *comms, gpu_state *gs, gpu_probe_exchange **xs,
-                           float **bufs, int G, uint64_t max_bytes, int *ok_out) {
+static int check_allreduce(const options *o, int use_nccl, const char *impl, nccl_api *nc, ncclComm_t *comms, gpu_state *gs,
+                           gpu_probe_exchange **xs, float **bufs, int G, uint64_t max_bytes, int *ok_out) {
   enum { CHECK_ELEMS = (1 << 18) + 3 };
   int rc;
   float *h = (float *)malloc(sizeof(float) * CHECK_ELEMS);
@@ -602,7 +615,7 @@ static int check_allreduce(const options *o, int use_nccl, nccl_api *nc, ncclCom
   }
   free(h);
   printf("RESULT kind=allreduce_check gpus=%d gpu=all bytes=%" PRIu64 " ms=na ms_med=na gbs=na frac_nominal=na "
-         "frac_measured=na lanes=na match=%d impl=%s\n", G, 4 * celems, ok, use_nccl ? "nccl" : "p2p_kernel");
+         "frac_measured=na lanes=na match=%d impl=%s\n", G, 4 * celems, ok, impl);
   if (!ok) fail(RC_PARITY);
   *ok_out = ok;
   return 0;
@@ -636,12 +649,56 @@ static int phase_sweep(const options *o, gpu_state *gs, int ng, nccl_api *nc) {
     }
     if (nc->so) NC(nc, nc->CommInitAll(comms, G, devs));
 
-    for (int use_nccl = nc->so ? 1 : 0; use_nccl >= 0; --use_nccl) {
+    /* Four columns on the same sizes.  NCCL three ways -- on the probe's own segment as it is
+     * (plain: NCCL stages through its own buffers), on ncclMemAlloc'd memory registered with
+     * ncclCommRegister (zero-copy / NVLS user buffers) and, where the library has it,
+     * registered as a symmetric window (NCCL 2.27) -- and the probe's one-kernel allreduce (K4). */
+    enum { I_NCCL, I_NCCL_REG, I_NCCL_SYM, I_OWN, I_COUNT };
+    static const char *impl_name[I_COUNT] = {"nccl", "nccl_registered", "nccl_symmetric", "p2p_kernel"};
+    for (int impl = nc->so ? I_NCCL : I_OWN; impl < I_COUNT; ++impl) {
+      const int use_nccl = impl != I_OWN;
+      float *nbufs[MAX_GPUS] = {0};
+      void *regs[MAX_GPUS] = {0};
+      ncclWindow_t wins[MAX_GPUS] = {0};
+      float **use = bufs;
+      if (impl == I_NCCL_REG || impl == I_NCCL_SYM) {
+        int ok = nc->MemAlloc && nc->MemFree &&
+                 (impl == I_NCCL_REG ? (nc->CommRegister && nc->CommDeregister) : (nc->CommWindowRegister && nc->CommWindowDeregister));
+        for (int d = 0; d < G && ok; ++d) {
+          CU(cudaSetDevice(gs[d].dev));
+          if (nc->MemAlloc((void **)&nbufs[d], max_bytes) != ncclSuccess) ok = 0;
+        }
+        if (ok && impl == I_NCCL_REG)
+          for (int d = 0; d < G && ok; ++d) {
+            CU(cudaSetDevice(gs[d].dev));
+            if (nc->CommRegister(comms[d], nbufs[d], max_bytes, &regs[d]) != ncclSuccess) ok = 0;
+          }
+        if (ok && impl == I_NCCL_SYM) { /* collective: every rank of the communicator registers, grouped in one process */
+          ok = nc->GroupStart() == ncclSuccess;
+          for (int d = 0; d < G && ok; ++d) {
+            CU(cudaSetDevice(gs[d].dev));
+            if (nc->CommWindowRegister(comms[d], nbufs[d], max_bytes, &wins[d], NCCL_WIN_COLL_SYMMETRIC) != ncclSuccess) ok = 0;
+          }
+          if (nc->GroupEnd() != ncclSuccess) ok = 0;
+        }
+        printf("PROBE INFO allreduce_buffers gpus=%d impl=%s available=%d\n", G, impl_name[impl], ok);
+        if (!ok) { /* an older NCCL, or a fabric that refuses: the column is absent, not a failure */
+          cudaGetLastError();
+          for (int d = 0; d < G; ++d) {
+            CU(cudaSetDevice(gs[d].dev));
+            if (regs[d]) nc->CommDeregister(comms[d], regs[d]);
+            if (wins[d]) nc->CommWindowDeregister(comms[d], wins[d]);
+            if (nbufs[d]) nc->MemFree(nbufs[d]);
+          }
+          continue;
+        }
+        use = nbufs;
+      }
       int ok = 0;
-      if ((rc = check_allreduce(o, use_nccl, nc, comms, gs, xs, bufs, G, max_bytes, &ok))) return rc;
+      if ((rc = check_allreduce(o, use_nccl, impl_name[impl], nc, comms, gs, xs, use, G, max_bytes, &ok))) return rc;
       for (int d = 0; d < G; ++d) { /* zeros: sums stay finite however often the prefix is reduced */
         CU(cudaSetDevice(gs[d].dev));
-        CU(cudaMemsetAsync(bufs[d], 0, max_bytes, gs[d].st));
+        CU(cudaMemsetAsync(use[d], 0, max_bytes, gs[d].st));
       }
       double best_bus = 0;
       uint64_t best_bytes = 0;
@@ -649,18 +706,31 @@ static int phase_sweep(const options *o, gpu_state *gs, int ng, nccl_api *nc) {
         const int iters = S >= (1u << 20) ? o->iters : 2 * o->iters;
         double ms = 0;
         if (!use_nccl && o->allreduce_algo == GPU_PROBE_ALLREDUCE_PUSH && S > (2u << 20)) break; /* one-shot limit */
-        if ((rc = time_allreduce(o, use_nccl, nc, comms, gs, xs, bufs, G, S, iters, &ms))) return rc;
+        if ((rc = time_allreduce(o, use_nccl, nc, comms, gs, xs, use, G, S, iters, &ms))) return rc;
         const double algbw = (double)S / (ms * 1e-3) / 1e9;
         const double busbw = algbw * 2.0 * (G - 1) / G;
         if (busbw > best_bus) { best_bus = busbw; best_bytes = S; }
         printf("RESULT kind=allreduce gpus=%d gpu=all bytes=%" PRIu64 " ms=%.5f ms_med=%.5f gbs=%.2f "
                "frac_nominal=%.4f frac_measured=na lanes=na match=na us=%.2f algbw=%.2f busbw=%.2f impl=%s\n",
-               G, S, ms, ms, busbw, busbw / NOMINAL_NVLINK_GBS, ms * 1e3, algbw, busbw,
-               use_nccl ? "nccl" : "p2p_kernel");
+               G, S, ms, ms, busbw, busbw / NOMINAL_NVLINK_GBS, ms * 1e3, algbw, busbw, impl_name[impl]);
       }
       printf("RESULT kind=allreduce_peak gpus=%d gpu=all bytes=%" PRIu64 " ms=na ms_med=na gbs=%.2f frac_nominal=%.4f "
              "frac_measured=na lanes=na match=na impl=%s\n", G, best_bytes, best_bus, best_bus / NOMINAL_NVLINK_GBS,
-             use_nccl ? "nccl" : "p2p_kernel");
+             impl_name[impl]);
+      if (use == nbufs) {
+        if ((rc = sync_all(gs, G))) return rc;
+        if (impl == I_NCCL_SYM) NC(nc, nc->GroupStart());
+        for (int d = 0; d < G; ++d) {
+          CU(cudaSetDevice(gs[d].dev));
+          if (regs[d]) NC(nc, nc->CommDeregister(comms[d], regs[d]));
+          if (wins[d]) NC(nc, nc->CommWindowDeregister(comms[d], wins[d]));
+        }
+        if (impl == I_NCCL_SYM) NC(nc, nc->GroupEnd());
+        for (int d = 0; d < G; ++d) {
+          CU(cudaSetDevice(gs[d].dev));
+          NC(nc, nc->MemFree(nbufs[d]));
+        }
+      }
     }
     if (nc->so)
       for (int d = 0; d < G; ++d) NC(nc, nc->CommDestroy(comms[d]));

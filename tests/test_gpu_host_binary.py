@@ -108,7 +108,11 @@ def test_multi_gpu_probe_sharded_checksum_sweep_and_p2p():
     for x in combos.values():
         assert x["lanes"] == hexw and x["match"] == "1"
     assert all(x["match"] == "1" for x in by["allreduce_check"])
-    assert {x["impl"] for x in by["allreduce_check"]} == {"nccl", "p2p_kernel"}
+    impls = {x["impl"] for x in by["allreduce_check"]}
+    assert {"nccl", "p2p_kernel"} <= impls <= {"nccl", "nccl_registered", "nccl_symmetric", "p2p_kernel"}
+    # the registered columns appear whenever the loaded NCCL can register buffers, and then they are checked too
+    for impl in impls:
+        assert [int(x["bytes"]) for x in by["allreduce"] if x["gpus"] == "2" and x["impl"] == impl] == [1 << k for k in range(10, 27)]
     for impl in ("nccl", "p2p_kernel"):
         sizes = [int(x["bytes"]) for x in by["allreduce"] if x["gpus"] == "2" and x["impl"] == impl]
         assert sizes == [1 << k for k in range(10, 27)], impl

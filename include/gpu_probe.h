@@ -147,7 +147,9 @@ int gpu_probe_checksum_u64(const uint64_t *w, uint64_t n, uint64_t first_index,
  *    one kernel on `stream`.
  *  - the first call on each device looks the array's device address up (a one-time
  *    driver query that may also load the library's device code): make that first
- *    call before starting any stream capture on that device.
+ *    call before starting any stream capture on that device.  The address is remembered
+ *    for the life of the process: a host that calls cudaDeviceReset() destroys the array
+ *    the remembered address points at, and must not call this entry point afterwards.
  *  - all calls on a device share the one array, which still holds what the previous
  *    call wrote; the entry point re-zeroes the only word that must start at zero.
  *    Two calls that overlap on the GPU (different streams, no ordering) race on it

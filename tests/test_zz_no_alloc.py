@@ -80,3 +80,26 @@ def test_noalloc_edge_sizes_and_limit():
     assert rc == gpuprobe.ETOOBIG
     assert "maximum" in gpuprobe.error_string(rc)
     assert gpuprobe.lib().gpu_probe_checksum_u64_noalloc(d.data_ptr(), 3, 0, None, None) == gpuprobe.EINVAL
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs: the scratch address is looked up per device")
+def test_noalloc_on_a_second_device_and_back():
+    """Every GPU holds its own copy of the built-in scratch, at an address the library looks up the
+    first time the entry point runs with that GPU current.  Device 0, then device 1, then device 0
+    again -- each against the CPU oracle, so an address cached for the wrong device (the kernel
+    would read another GPU's ticket word, or fault) cannot pass."""
+    rng = np.random.default_rng(7)
+    n, first = 148 * 4096 * 2 + 33, (1 << 35) + 1
+    w = rng.integers(0, 1 << 64, size=n, dtype=np.uint64)
+    want = oracle.checksum_u64(w, first)
+    try:
+        for dev in (0, 1, 0, 1):
+            with torch.cuda.device(dev):
+                d = from_np(w)
+                out = lanes_buf()
+                gpuprobe.checksum_u64_noalloc(d.data_ptr(), n, first, out.data_ptr(), stream())
+                gpuprobe.checksum_u64_noalloc(d.data_ptr(), n, first, out.data_ptr(), stream())  # twice in a row here too
+                torch.cuda.synchronize()
+                assert lanes_of(out) == want, dev
+    finally:
+        torch.cuda.set_device(0)

@@ -721,6 +721,24 @@ static int persistent_grid(K kernel, size_t dyn_smem, uint64_t tiles, unsigned *
   return 0;
 }
 
+static inline int env_or(const char *name, int fallback) {
+  const char *e = getenv(name);
+  return e ? atoi(e) : fallback;
+}
+
+// True when dst or src is memory of a GPU other than the current one (a peer mapping).
+static bool crosses_nvlink(const void *dst, const void *src) {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) return false;
+  const void *ptrs[2] = {dst, src};
+  for (const void *p : ptrs) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); continue; }
+    if (at.type == cudaMemoryTypeDevice && at.device != dev) return true;
+  }
+  return false;
+}
+
 static inline bool aligned(const void *p, size_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
 static inline int launch_rc() { return int(cudaGetLastError()); }
 
@@ -753,6 +771,9 @@ constexpr int kChecksumPaceNs = 650;
 // 8/SM: 6100-6300), read-only wants more (checksum: 6/SM -> 7350 GB/s).
 constexpr int kCopyTileBytes = 32 * 1024, kCopyStages = 3;
 constexpr int kCopyPaceNs = 1426;  // one 32 KiB tile (64 KiB of traffic) per SM per 1426 ns = 6800 GB/s asked for; GPU_PROBE_COPY_PACE_NS=0: unpaced
+// the same ring when the copy crosses NVLink (one side is a peer GPU's memory): CTAs and the rate asked of the link
+constexpr int kCopyPeerCtas = 0;   // 0: one CTA per SM
+constexpr int kCopyPeerGBs = 0;    // 0: unpaced
 constexpr int kLdgTriadCtasPerSm = 2;
 constexpr int kLdgChecksumCtasPerSm = 6;
 
@@ -1181,18 +1202,29 @@ int gpu_probe_p2p_copy(void *dst, const void *src, uint64_t bytes, void *stream)
   unsigned grid = 1;
   int rc;
   // Large aligned copies: the TMA ring (32 KiB tiles x 3 stages, 1 CTA/SM = 96 KiB in flight per
-  // SM) measured 6470 GB/s locally against 5835 for the LDG/STG kernel; to a peer both sit at the
-  // same 711 GB/s (the copy engine reaches 779), so the choice only matters on the HBM side
-  // (tools/tune_copy.py, profiles/tune_copy_r1.log).  Small copies keep the LDG kernel: a ring
-  // needs a few tiles per CTA to fill.
+  // SM) measured 6470 GB/s locally against 5835 for the LDG/STG kernel (tools/tune_copy.py,
+  // profiles/tune_copy_r1.log).  Small copies keep the LDG kernel: a ring needs a few tiles per CTA
+  // to fill.  When either side lives on ANOTHER GPU the bound is the NVLink rate, an order of
+  // magnitude below HBM: the same ring then runs with the peer geometry below (fewer CTAs, refills
+  // paced for the link, not for HBM).
   if (aligned(dst, 16) && aligned(src, 16) && bytes >= (uint64_t(8) << 20)) {
     auto k = copy_tma<kCopyTileBytes, kCopyStages>;
     constexpr size_t smem = size_t(kCopyTileBytes) * kCopyStages + sizeof(uint64_t) * kCopyStages;
     int occ = 0, sms = 0;
     if ((rc = kernel_facts(reinterpret_cast<const void *>(k), smem, 32, &occ, &sms))) return rc;
     uint64_t g = uint64_t(sms), tiles = bytes / kCopyTileBytes;
+    static const int hbm_pace_ns = [] { const char *e = getenv("GPU_PROBE_COPY_PACE_NS"); return e ? atoi(e) : kCopyPaceNs; }();
+    int pace_ns = hbm_pace_ns;
+    if (crosses_nvlink(dst, src)) {
+      static const bool tune = getenv("GPU_PROBE_TUNE") != nullptr;  // dev knob: re-read the two settings on every call
+      static int peer_ctas = env_or("GPU_PROBE_COPY_PEER_CTAS", kCopyPeerCtas);
+      static int peer_gbs = env_or("GPU_PROBE_COPY_PEER_GBS", kCopyPeerGBs);
+      if (tune) { peer_ctas = env_or("GPU_PROBE_COPY_PEER_CTAS", kCopyPeerCtas); peer_gbs = env_or("GPU_PROBE_COPY_PEER_GBS", kCopyPeerGBs); }
+      if (peer_ctas > 0) g = uint64_t(peer_ctas) < uint64_t(sms) * uint64_t(occ) ? uint64_t(peer_ctas) : uint64_t(sms) * uint64_t(occ);
+      // every CTA refills one 32 KiB tile per pace: ctas x 32 KiB / pace = the rate asked of the link
+      pace_ns = peer_gbs > 0 ? int(uint64_t(kCopyTileBytes) * g / uint64_t(peer_gbs)) : 0;
+    }
     if (g > tiles) g = tiles;
-    static const int pace_ns = [] { const char *e = getenv("GPU_PROBE_COPY_PACE_NS"); return e ? atoi(e) : kCopyPaceNs; }();
     k<<<unsigned(g), 32, smem, st>>>(static_cast<unsigned char *>(dst), static_cast<const unsigned char *>(src), bytes, pace_ns);
     return launch_rc();
   }

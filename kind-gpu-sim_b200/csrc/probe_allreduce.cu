@@ -41,6 +41,7 @@ struct AllreduceArgs {
   uint64_t count;         // fp32 elements
   uint64_t stage_bytes;   // one staging slot (one-shot algorithm); staging = segment + kHeaderBytes
   unsigned char *mc;      // NVSwitch multicast alias of ALL ranks' segments (same layout), or null
+  uint64_t push_call;     // one-shot algorithm: number of this call on the exchange, 1, 2, ... (host-side counter)
 };
 
 __device__ __forceinline__ float4 ld_peer(const float4 *p) {  // system-coherent, never from a stale L1 line
@@ -231,13 +232,13 @@ allreduce_f32_multimem_kernel(const AllreduceArgs a) {
 // plus the fence.  Every rank computes every element itself, in rank order, so the ranks
 // still agree bit for bit.  Staging is double-buffered by call parity (same argument as the
 // lanes mailbox), so no trailing barrier is needed; peers never read the operand itself.
+// The parity comes from ONE counter per exchange, kept by the host and identical in every CTA of
+// every rank (all ranks make the same sequence of calls).  A per-CTA count would let CTAs of
+// consecutive calls with different grids disagree about which staging buffer a vector lives in.
 template <int G, int U>
 __device__ __forceinline__ void push_body(const AllreduceArgs &a) {
   uint64_t *hdr = reinterpret_cast<uint64_t *>(a.seg[a.rank]);
-  __shared__ uint64_t epoch0;
-  if (threadIdx.x == 0) epoch0 = hdr[kPushEpochOffsetWords + blockIdx.x];
-  __syncthreads();
-  const uint64_t e = epoch0 + 1;
+  const uint64_t e = a.push_call;  // flags only ever grow: a CTA that sat out smaller calls simply jumps ahead
   const size_t slot_set = kHeaderBytes + size_t(e & 1) * G * a.stage_bytes;  // staging[e & 1]
   float4 *mine_op = reinterpret_cast<float4 *>(a.seg[a.rank] + a.operand_off);
   const uint64_t nvec = (a.count + 3) / 4;  // the operand is padded to 16 bytes inside the buffer (see entry point)
@@ -276,10 +277,7 @@ __device__ __forceinline__ void push_body(const AllreduceArgs &a) {
       }
     }
   }
-  if (threadIdx.x == 0) {
-    hdr[kPushEpochOffsetWords + blockIdx.x] = e;
-    if (!ok) hdr[1] = 1;
-  }
+  if (threadIdx.x == 0 && !ok) hdr[1] = 1;
 }
 
 template <int G, int U>
@@ -417,6 +415,7 @@ extern "C" int gpu_probe_allreduce_f32(gpu_probe_exchange *x, uint64_t offset_by
   int rc = plan_allreduce(x, offset_bytes, count, &algo, ctas, &a, &grid);
   if (rc) return rc;
   if (count == 0) return 0;  // every rank passes the same count, so every rank skips
+  if (algo == GPU_PROBE_ALLREDUCE_PUSH) a.push_call = ++x->push_calls;  // counted only once nothing can fail any more
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (x->world) {
     case 1: return launch_allreduce<1>(a, algo, grid, st);
@@ -463,6 +462,8 @@ extern "C" int gpu_probe_allreduce_f32_group(gpu_probe_exchange *const *xs, int 
     else if (algo_r != algo0 || grid_r != grid) return GPU_PROBE_EINVAL;
   }
   if (count == 0) return 0;
+  if (algo0 == GPU_PROBE_ALLREDUCE_PUSH)
+    for (int r = 0; r < world; ++r) ga.r[r].push_call = ++xs[r]->push_calls;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (world) {
     case 1: return launch_group<1>(ga, algo0, grid, st);

@@ -127,7 +127,7 @@ constexpr size_t kWorkspaceBytes =
 //                    call k+2 after every peer has written call k+1, which each peer does
 //                    after it finished reading call k.
 //   8 KiB   cta_epoch[kMaxCommCtas]           barrier epoch of CTA b on this GPU (local only)
-//   16 KiB  push_epoch[kMaxCommCtas]          call count of CTA b in the one-shot allreduce (local)
+//   16 KiB  (unused since round 2: the one-shot allreduce's call count lives on the host)
 //   32 KiB  flags[kMaxCommCtas][kMaxRanks]    flags[b][p] = last barrier epoch CTA b of rank p
 //                                             signalled to this GPU (written by p, polled here)
 //   160 KiB push_flags[kMaxCommCtas][kMaxRanks]  same, for the one-shot allreduce

@@ -36,6 +36,7 @@ struct gpu_probe_exchange {
   int sock;
   char sock_name[40];
   unsigned long long timeout_ns;
+  uint64_t push_calls;          // one-shot allreduce calls issued on this exchange (staging parity, flag epoch)
 };
 
 static constexpr uint32_t kXMagic = 0x58434847u;  // "XCHG"

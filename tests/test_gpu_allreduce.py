@@ -167,6 +167,39 @@ def test_allreduce_grid_choices_agree():
         G.close()
 
 
+def test_one_shot_push_with_a_grid_that_changes_between_calls():
+    """Consecutive one-shot calls on one exchange with DIFFERENT explicit grids: vector i then moves
+    from one CTA to another between calls.  The staging buffer of a call is chosen by the parity of a
+    per-exchange call counter, the same in every CTA -- with a per-CTA count (round 1) CTA 1 of the
+    second call below would have written into the buffer the peer's CTA 0 was still reading."""
+    world, count = 2, 4096  # 1024 vectors: ctas=1 covers them with 2 per thread, ctas=2 with one each
+    rng = np.random.default_rng(5)
+    G = Group(world, 4 * count)
+    try:
+        for call, ctas in enumerate([1, 2, 1, 2, 2, 1, 4, 1, 2, 8, 1]):
+            parts = [rng.standard_normal(count).astype(np.float32) for _ in range(world)]
+            want = rank_order_sum(parts)
+            for r in range(world):
+                G.put(r, parts[r])
+            G.allreduce(count, 0, ctas, gpuprobe.ALLREDUCE_PUSH)
+            G.sync()
+            for r in range(world):
+                assert np.array_equal(G.get(r, count).view(np.uint32), want.view(np.uint32)), (call, ctas, r)
+        # and back to back without a host sync in between: each call's input is the previous call's output
+        parts = [np.full(count, float(r + 1), dtype=np.float32) for r in range(world)]
+        for r in range(world):
+            G.put(r, parts[r])
+        for ctas in (1, 2, 1, 4, 2, 1):
+            G.allreduce(count, 0, ctas, gpuprobe.ALLREDUCE_PUSH)
+        G.sync()
+        want = np.full(count, 3.0 * 2 ** 5, dtype=np.float32)  # (1 + 2) doubled by each of the five further calls
+        for r in range(world):
+            assert np.array_equal(G.get(r, count), want), r
+            assert G.x[r].status() == 0
+    finally:
+        G.close()
+
+
 def test_allreduce_argument_errors_and_missing_peer():
     G = Group(2, 1 << 16)
     try:

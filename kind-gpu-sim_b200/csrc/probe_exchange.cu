@@ -36,6 +36,7 @@
 #include <atomic>
 #include <mutex>
 #include <new>
+#include <sys/random.h>
 #include <sys/socket.h>
 #include <sys/time.h>
 #include <sys/un.h>
@@ -163,7 +164,11 @@ void unmap_segment(const DriverApi *d, void *va, size_t bytes) {
 // ---------------------------------------------------------------------------
 enum MsgType : int32_t { MSG_MEM = 1, MSG_MC = 2, MSG_MC_NONE = 3, MSG_ADDED = 4, MSG_ADD_FAILED = 5, MSG_BOUND = 6,
                          MSG_BIND_FAILED = 7 };
-struct Msg { uint32_t magic; int32_t type; int32_t rank; int32_t pad; };
+// `token` is the RECEIVER's secret from its exported handle: only a process that was given the
+// handles over the host's own channel can name it.  The kernel also tells the receiver who sent
+// each datagram (SO_PASSCRED), so a message is taken only from the user and -- when the ranks
+// share a PID namespace -- the very process that exported handle `rank`.
+struct Msg { uint32_t magic; int32_t type; int32_t rank; int32_t pad; uint64_t token; };
 constexpr uint32_t kMsgMagic = 0x47505845u;
 
 socklen_t abstract_addr(sockaddr_un *a, const char *name) {
@@ -174,8 +179,8 @@ socklen_t abstract_addr(sockaddr_un *a, const char *name) {
   return socklen_t(offsetof(sockaddr_un, sun_path) + 1 + n);
 }
 
-int send_msg(int sock, const char *to, int type, int rank, int fd) {
-  Msg m{kMsgMagic, type, rank, 0};
+int send_msg(int sock, const char *to, uint64_t to_token, int type, int rank, int fd) {
+  Msg m{kMsgMagic, type, rank, 0, to_token};
   sockaddr_un addr;
   const socklen_t alen = abstract_addr(&addr, to);
   iovec iov{&m, sizeof(m)};
@@ -204,10 +209,12 @@ int send_msg(int sock, const char *to, int type, int rank, int fd) {
   return int(cudaErrorSystemNotReady);
 }
 
-int recv_msg(int sock, Msg *m, int *fd) {
+int recv_msg(int sock, Msg *m, int *fd, pid_t *from_pid, uid_t *from_uid) {
   *fd = -1;
+  *from_pid = 0;
+  *from_uid = uid_t(-1);
   iovec iov{m, sizeof(*m)};
-  alignas(cmsghdr) char ctrl[CMSG_SPACE(sizeof(int))];
+  alignas(cmsghdr) char ctrl[CMSG_SPACE(sizeof(int)) + CMSG_SPACE(sizeof(ucred))];
   msghdr h;
   std::memset(&h, 0, sizeof(h));
   h.msg_iov = &iov;
@@ -216,9 +223,18 @@ int recv_msg(int sock, Msg *m, int *fd) {
   h.msg_controllen = sizeof(ctrl);
   ssize_t n;
   do { n = recvmsg(sock, &h, 0); } while (n < 0 && errno == EINTR);
-  if (n != ssize_t(sizeof(*m)) || m->magic != kMsgMagic) return GPU_PROBE_ETIMEDOUT;  // SO_RCVTIMEO ran out
-  for (cmsghdr *c = CMSG_FIRSTHDR(&h); c; c = CMSG_NXTHDR(&h, c))
-    if (c->cmsg_level == SOL_SOCKET && c->cmsg_type == SCM_RIGHTS) std::memcpy(fd, CMSG_DATA(c), sizeof(int));
+  if (n < 0) return GPU_PROBE_ETIMEDOUT;  // SO_RCVTIMEO ran out
+  for (cmsghdr *c = CMSG_FIRSTHDR(&h); c; c = CMSG_NXTHDR(&h, c)) {
+    if (c->cmsg_level != SOL_SOCKET) continue;
+    if (c->cmsg_type == SCM_RIGHTS) std::memcpy(fd, CMSG_DATA(c), sizeof(int));
+    if (c->cmsg_type == SCM_CREDENTIALS) {
+      ucred u;
+      std::memcpy(&u, CMSG_DATA(c), sizeof(u));
+      *from_pid = u.pid;
+      *from_uid = u.uid;
+    }
+  }
+  if (n != ssize_t(sizeof(*m)) || m->magic != kMsgMagic) m->type = 0;  // not one of ours: the caller drops it (and its fd)
   return 0;
 }
 
@@ -226,7 +242,8 @@ struct WireHandle {  // the 64 opaque bytes of gpu_probe_exchange_export
   uint32_t magic;
   int32_t rank, mc_supported, pid;
   uint64_t seg_bytes;
-  char name[40];
+  uint64_t token;  // random per exchange; every message TO this rank must carry it
+  char name[32];
 };
 static_assert(sizeof(WireHandle) == GPU_PROBE_EXCHANGE_HANDLE_BYTES, "wire handle must fill the 64 bytes exactly");
 
@@ -435,12 +452,17 @@ extern "C" int gpu_probe_exchange_export(gpu_probe_exchange *x, unsigned char ha
     sockaddr_un addr;
     const socklen_t alen = abstract_addr(&addr, x->sock_name);
     timeval tv{30, 0};  // nobody waits for a lost rank for ever
-    if (bind(s, reinterpret_cast<sockaddr *>(&addr), alen) != 0 ||
-        setsockopt(s, SOL_SOCKET, SO_RCVTIMEO, &tv, sizeof(tv)) != 0) {
+    const int on = 1;
+    uint64_t token = 0;
+    if (getrandom(&token, sizeof(token), 0) != ssize_t(sizeof(token)) ||
+        bind(s, reinterpret_cast<sockaddr *>(&addr), alen) != 0 ||
+        setsockopt(s, SOL_SOCKET, SO_RCVTIMEO, &tv, sizeof(tv)) != 0 ||
+        setsockopt(s, SOL_SOCKET, SO_PASSCRED, &on, sizeof(on)) != 0) {
       close(s);
       return int(cudaErrorSystemNotReady);
     }
     x->sock = s;
+    x->token = token;
   }
   WireHandle w;
   std::memset(&w, 0, sizeof(w));
@@ -449,6 +471,7 @@ extern "C" int gpu_probe_exchange_export(gpu_probe_exchange *x, unsigned char ha
   w.mc_supported = x->mc_supported ? 1 : 0;
   w.pid = int(getpid());
   w.seg_bytes = x->seg_bytes;
+  w.token = x->token;
   std::memcpy(w.name, x->sock_name, sizeof(w.name));
   std::memcpy(handle, &w, sizeof(w));
   return 0;
@@ -480,7 +503,7 @@ extern "C" int gpu_probe_exchange_connect_ipc(gpu_probe_exchange *x, const unsig
   CUresult r = d->MemExportToShareableHandle(&myfd, x->mem, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0);
   if (r != CUDA_SUCCESS) return cu(r);
   for (int p = 0; p < world && rc == 0; ++p)
-    if (p != me) rc = send_msg(x->sock, w[p].name, MSG_MEM, me, myfd);
+    if (p != me) rc = send_msg(x->sock, w[p].name, w[p].token, MSG_MEM, me, myfd);
   close(myfd);
   if (rc) return rc;
   bool have_mc = false;
@@ -498,7 +521,7 @@ extern "C" int gpu_probe_exchange_connect_ipc(gpu_probe_exchange *x, const unsig
       have_mc = false;
     }
     for (int p = 1; p < world && rc == 0; ++p)
-      rc = send_msg(x->sock, w[p].name, have_mc ? MSG_MC : MSG_MC_NONE, me, have_mc ? mcfd : -1);
+      rc = send_msg(x->sock, w[p].name, w[p].token, have_mc ? MSG_MC : MSG_MC_NONE, me, have_mc ? mcfd : -1);
     if (mcfd >= 0) close(mcfd);
     if (rc) return rc;
   }
@@ -511,14 +534,25 @@ extern "C" int gpu_probe_exchange_connect_ipc(gpu_probe_exchange *x, const unsig
   auto pump = [&]() -> int {  // one message
     Msg m;
     int fd = -1;
-    int prc = recv_msg(x->sock, &m, &fd);
+    pid_t from_pid = 0;
+    uid_t from_uid = uid_t(-1);
+    int prc = recv_msg(x->sock, &m, &fd, &from_pid, &from_uid);
     if (prc) return prc;
+    // Only the peers this rank was told about may speak: right secret, a rank of this exchange, this
+    // user, and the exporting process itself (pid 0: the sender lives in another PID namespace, which
+    // the kernel cannot name here -- the secret and the uid still have to match).
+    const bool known = m.type != 0 && m.token == x->token && m.rank >= 0 && m.rank < world && m.rank != me &&
+                       from_uid == geteuid() && (from_pid == 0 || from_pid == pid_t(w[m.rank].pid));
+    if (!known) {
+      if (fd >= 0) close(fd);
+      return 0;  // a stranger's datagram: dropped, never acted on; the wait for the real peers goes on
+    }
     switch (m.type) {
       case MSG_MEM:
         if (m.rank >= 0 && m.rank < world && m.rank != me && mem_fd[m.rank] < 0 && fd >= 0) { mem_fd[m.rank] = fd; ++n_mem; fd = -1; }
         break;
-      case MSG_MC: if (fd >= 0) { mc_fd = fd; fd = -1; have_mc = true; } mc_decided = true; break;
-      case MSG_MC_NONE: mc_decided = true; break;
+      case MSG_MC: if (m.rank != 0 || mc_decided) break; if (fd >= 0) { mc_fd = fd; fd = -1; have_mc = true; } mc_decided = true; break;  // rank 0 owns the multicast object
+      case MSG_MC_NONE: if (m.rank == 0) mc_decided = true; break;
       case MSG_ADDED: ++n_added; break;
       case MSG_ADD_FAILED: ++n_add_failed; break;
       case MSG_BOUND: ++n_bound; break;
@@ -553,7 +587,7 @@ extern "C" int gpu_probe_exchange_connect_ipc(gpu_probe_exchange *x, const unsig
     const bool holding = ok;
     if (ok) ok = d->MulticastAddDevice(mch, cudev) == CUDA_SUCCESS;
     for (int p = 0; p < world && rc == 0; ++p)
-      if (p != me) rc = send_msg(x->sock, w[p].name, ok ? MSG_ADDED : MSG_ADD_FAILED, me, -1);
+      if (p != me) rc = send_msg(x->sock, w[p].name, w[p].token, ok ? MSG_ADDED : MSG_ADD_FAILED, me, -1);
     while (rc == 0 && n_added + n_add_failed < world - 1) rc = pump();
     bool all = ok && n_add_failed == 0 && rc == 0;
     bool bound = false;
@@ -563,7 +597,7 @@ extern "C" int gpu_probe_exchange_connect_ipc(gpu_probe_exchange *x, const unsig
       all = bound && map_segment(d, mch, x->seg_bytes, &x->device, 1, &va) == 0;
     }
     for (int p = 0; p < world && rc == 0; ++p)
-      if (p != me) rc = send_msg(x->sock, w[p].name, all ? MSG_BOUND : MSG_BIND_FAILED, me, -1);
+      if (p != me) rc = send_msg(x->sock, w[p].name, w[p].token, all ? MSG_BOUND : MSG_BIND_FAILED, me, -1);
     while (rc == 0 && n_bound + n_bind_failed < world - 1) rc = pump();
     int *refs = (all && n_bind_failed == 0 && rc == 0) ? new (std::nothrow) int(1) : nullptr;
     if (refs) {

@@ -34,7 +34,8 @@ struct gpu_probe_exchange {
   unsigned char *mc_base;       // multicast alias of the segments (same layout)
   // one process per GPU: handles travel as file descriptors over a unix datagram socket
   int sock;
-  char sock_name[40];
+  char sock_name[32];
+  uint64_t token;               // this rank's secret: travels inside the exported handle, demanded of every message
   unsigned long long timeout_ns;
   uint64_t push_calls;          // one-shot allreduce calls issued on this exchange (staging parity, flag epoch)
 };

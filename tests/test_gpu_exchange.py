@@ -202,3 +202,13 @@ def test_exchange_across_processes_over_ipc():
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert f"EXCHANGE_IPC_OK world={world}" in r.stdout
+
+
+def test_ipc_rendezvous_ignores_strangers():
+    """Two processes, both on cuda:0 (only the rendezvous runs, so one GPU is enough): forged
+    datagrams on a rank's socket -- no secret, a wrong secret, the peer's secret -- are dropped."""
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", "29578", os.path.join(ROOT, "tests", "mp_connect_worker.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "CONNECT_OK world=2" in r.stdout

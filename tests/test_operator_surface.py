@@ -206,6 +206,8 @@ def test_probe_pod_manifests_keep_the_scheduling_contract(name, gpus):
     assert "--bytes=4294967296" in cmd                      # BASELINE.json: 4 GiB arrays
     assert pod["spec"]["restartPolicy"] == "Never"
     assert pod["spec"]["tolerations"][0]["value"] == "true"  # a string, not the YAML boolean
+    env = {e["name"]: e["value"] for e in pod["spec"]["containers"][0]["env"]}
+    assert float(env["GPU_PROBE_MEASURED_HBM_GBS"]) > 0 and isinstance(env["GPU_PROBE_MEASURED_HBM_GBS"], str)
 
 
 def test_pod_runner_maps_the_image_path_and_reports_exit_code():

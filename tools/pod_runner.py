@@ -157,8 +157,13 @@ def run_beside(args, pod, cmd, gpus):
     sys.exit(max(runs["alone"]["rc"], runs["beside"]["rc"]))
 
 
+POD_ENV: dict = {}
+
+
 def container_of(pod: dict) -> tuple[list[str], int]:
     c = pod["spec"]["containers"][0]
+    POD_ENV.clear()
+    POD_ENV.update({e["name"]: str(e.get("value", "")) for e in c.get("env", []) if "name" in e})
     cmd = [str(x) for x in c.get("command", [])] + [str(x) for x in c.get("args", [])]
     gpus = int(c.get("resources", {}).get("limits", {}).get("nvidia.com/gpu", 0))
     return cmd, gpus
@@ -167,10 +172,11 @@ def container_of(pod: dict) -> tuple[list[str], int]:
 def run_one(cmd, gpus, first_gpu, extra, out):
     argv = [os.path.join(PROBE_ROOT, cmd[0][len("/probe/"):]) if cmd[0].startswith("/probe/") else cmd[0]] + cmd[1:] + extra
     env = dict(os.environ)
+    env.update(POD_ENV)  # the container's own `env:` entries, as the kubelet would set them
     env["CUDA_VISIBLE_DEVICES"] = ",".join(str(first_gpu + i) for i in range(gpus))
     peak = measured_hbm_gbs()
-    if peak and "GPU_PROBE_MEASURED_HBM_GBS" not in env:
-        env["GPU_PROBE_MEASURED_HBM_GBS"] = str(peak)  # so the pod's frac_measured column is filled in
+    if peak:
+        env["GPU_PROBE_MEASURED_HBM_GBS"] = str(peak)  # this box's own measurement beats the manifest's fleet figure
     t0 = time.time()
     p = subprocess.Popen(argv, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=env)
     first_result, lines = None, []

@@ -117,7 +117,7 @@ def test_multi_gpu_probe_sharded_checksum_sweep_and_p2p():
         sizes = [int(x["bytes"]) for x in by["allreduce"] if x["gpus"] == "2" and x["impl"] == impl]
         assert sizes == [1 << k for k in range(10, 27)], impl
     assert all(x["match"] == "1" for x in by["p2p"])
-    assert {x["mode"] for x in by["p2p"]} == {"sm_kernel", "copy_engine"}
+    assert {x["mode"] for x in by["p2p"]} == {"sm_kernel", "sm_kernel_pull", "copy_engine"}
 
 
 def _pod(*args):

@@ -530,7 +530,41 @@ def run_ours(args, rank, local_rank, world):
         dist.barrier()
         if xchg is not None:
             xchg.close()
+        del a, b, c
+        dist.barrier()
         dist.destroy_process_group()
+        if not args.no_restore and local_rank == 0:
+            restore_hbm_state(torch, world)
+
+
+def restore_hbm_state(torch, world, gib=64):
+    """Leave the GPUs as this run found them (rank 0 only, after every rank has left the job).
+
+    A multi-process run's collectives leave every GPU they touched 3.8 % short of its read+write
+    HBM bandwidth FOR THE NEXT PROCESS, for minutes (fresh-process triad 7030-7120 -> 6690 GB/s,
+    calibration verdict 1082 ns; read-only and write-only streams are unaffected, nothing NVML
+    reports moves).  What puts it back, every time it was tried, is a bulk peer transfer made by ONE
+    process that holds all the GPUs involved -- the host binary's P2P phase, its allreduce sweep to
+    1 GiB, a one-process K4 loop; the same copies issued by the ranks themselves (each from its own
+    process) only ever cured the GPU that received last (profiles/slow_state_r2.md section 4).
+    So once the process group is gone and the other ranks are exiting, rank 0 alone copies `gib` x
+    1 GiB with the copy engine from each GPU into its right-hand neighbour, one pair at a time:
+    0.1 s of traffic per GPU plus a context on each, after everything that is timed or reported."""
+    if world < 2 or torch.cuda.device_count() < world:
+        return
+    try:
+        time.sleep(1.5)  # the other ranks are on their way out
+        for d in range(world):
+            nxt = (d + 1) % world
+            src = torch.empty(1 << 30, dtype=torch.uint8, device=f"cuda:{d}")
+            dst = torch.empty(1 << 30, dtype=torch.uint8, device=f"cuda:{nxt}")
+            for _ in range(gib):
+                dst.copy_(src, non_blocking=True)
+            torch.cuda.synchronize(d)
+            torch.cuda.synchronize(nxt)
+            del src, dst
+    except Exception as e:  # hygiene only: never fail a finished measurement over it
+        print(f"bench.py: closing HBM-state pass skipped ({type(e).__name__}: {e})", file=sys.stderr)
 
 
 def run_e2e(args, gpuprobe, torch, b, c, n, first, want_lanes, dist, world):
@@ -669,6 +703,7 @@ def main():
                     help="N>1: how the 16-byte lanes are summed over ranks (fused P2P exchange, or NCCL)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / parity leg")
+    ap.add_argument("--no-restore", action="store_true", help="N>1: skip rank 0's closing copy-engine pass that puts the GPUs' HBM state back (see restore_hbm_state)")
     ap.add_argument("--no-clocks", action="store_true", help="ablation only: do not sample NVML clocks while timing")
     ap.add_argument("--clock-period-ms", type=float, default=5.0, help="NVML sampling period during the timed region")
     args = ap.parse_args()

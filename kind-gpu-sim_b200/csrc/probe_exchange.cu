@@ -30,6 +30,7 @@
 #include <cerrno>
 #include <cstddef>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -292,7 +293,7 @@ extern "C" int gpu_probe_exchange_create(gpu_probe_exchange **out, int rank, int
       mc = 0;
     }
   }
-  x->mc_supported = mc != 0;
+  x->mc_supported = mc != 0 && getenv("GPU_PROBE_NO_MULTICAST") == nullptr;  // dev knob: plain peer mappings only
   if (r == CUDA_SUCCESS) {
     if (gran == 0) gran = 2u << 20;
     x->seg_bytes = ((x->payload_offset + buffer_bytes + gran - 1) / gran) * gran;

@@ -23,7 +23,7 @@ import gpuprobe  # noqa: E402
 
 def main():
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
-    torch.cuda.set_device(0)
+    torch.cuda.set_device(int(os.environ["LOCAL_RANK"]) if os.environ.get("GPU_PROBE_CONNECT_TWO_GPUS") else 0)
     dist.init_process_group("gloo")
     x = gpuprobe.Exchange(rank, world, 1 << 20)
     mine = x.export_handle()

@@ -146,6 +146,8 @@ def run_beside(args, pod, cmd, gpus):
             for p in procs:
                 p.wait()
         runs[label] = {"rc": out["rc"], "triad_GBps_per_gpu": triad_gbs(out["stdout"]),
+                       "triad_pace_ns_per_gpu": {ln.split("gpu=")[1].split()[0]: int(ln.split("pace_ns=")[1].split()[0])
+                                                 for ln in out["stdout"] if ln.startswith("PROBE INFO triad_calibrate")},
                        "launch_to_first_result_s": out["launch_to_first_result_s"],
                        "launch_to_exit_s": round(out["launch_to_exit_s"], 3),
                        "verdict": out["stdout"][-1] if out["stdout"] else "", "stderr_tail": out["stderr"][-400:]}

@@ -21,7 +21,9 @@ from __future__ import annotations
 import argparse
 import json
 import os
+import signal
 import statistics
+import subprocess
 import sys
 import threading
 import time
@@ -533,36 +535,30 @@ def run_ours(args, rank, local_rank, world):
         del a, b, c
         dist.barrier()
         dist.destroy_process_group()
-        if not args.no_restore and local_rank == 0:
-            restore_hbm_state(torch, world)
 
 
-def restore_hbm_state(torch, world, gib=64):
-    """Leave the GPUs as this run found them (rank 0 only, after every rank has left the job).
+def restore_hbm_state(world):
+    """Leave the GPUs as this run found them.  Runs in rank 0's PARENT process (see main): by now the
+    rank's worker -- the only process of this job that ever held a CUDA context here -- is gone.
 
     A multi-process run's collectives leave every GPU they touched 3.8 % short of its read+write
     HBM bandwidth FOR THE NEXT PROCESS, for minutes (fresh-process triad 7030-7120 -> 6690 GB/s,
     calibration verdict 1082 ns; read-only and write-only streams are unaffected, nothing NVML
-    reports moves).  What puts it back, every time it was tried, is a bulk peer transfer made by ONE
-    process that holds all the GPUs involved -- the host binary's P2P phase, its allreduce sweep to
-    1 GiB, a one-process K4 loop; the same copies issued by the ranks themselves (each from its own
-    process) only ever cured the GPU that received last (profiles/slow_state_r2.md section 4).
-    So once the process group is gone and the other ranks are exiting, rank 0 alone copies `gib` x
-    1 GiB with the copy engine from each GPU into its right-hand neighbour, one pair at a time:
-    0.1 s of traffic per GPU plus a context on each, after everything that is timed or reported."""
-    if world < 2 or torch.cuda.device_count() < world:
+    reports moves).  What puts it back, every time it was tried, is bulk peer traffic made by ONE
+    process that holds all the GPUs involved and is the last to touch them: the host binary's P2P
+    phase or its allreduce sweep to 1 GiB (profiles/slow_state_r2.md sections 3-4).  The same copies
+    issued from inside the job only cured the GPUs whose own rank was already gone.  So the cure is
+    the probe's own pod command on small arrays, run once after the job: a few seconds, after
+    everything that is timed or reported."""
+    exe = os.path.join(ROOT, "kind-gpu-sim_b200", "bin", "gpu-probe")
+    if world < 2 or not os.path.exists(exe):
         return
+    time.sleep(1.5)  # the other ranks are on their way out
     try:
-        time.sleep(1.5)  # the other ranks are on their way out
-        for d in range(world):
-            nxt = (d + 1) % world
-            src = torch.empty(1 << 30, dtype=torch.uint8, device=f"cuda:{d}")
-            dst = torch.empty(1 << 30, dtype=torch.uint8, device=f"cuda:{nxt}")
-            for _ in range(gib):
-                dst.copy_(src, non_blocking=True)
-            torch.cuda.synchronize(d)
-            torch.cuda.synchronize(nxt)
-            del src, dst
+        r = subprocess.run([exe, f"--max-gpus={world}", "--bytes=64m", "--iters=2", "--warmup=0"], capture_output=True,
+                           text=True, timeout=240)
+        if r.returncode != 0:
+            print(f"bench.py: closing HBM-state pass exited {r.returncode}: {r.stdout[-200:]} {r.stderr[-200:]}", file=sys.stderr)
     except Exception as e:  # hygiene only: never fail a finished measurement over it
         print(f"bench.py: closing HBM-state pass skipped ({type(e).__name__}: {e})", file=sys.stderr)
 
@@ -703,7 +699,7 @@ def main():
                     help="N>1: how the 16-byte lanes are summed over ranks (fused P2P exchange, or NCCL)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / parity leg")
-    ap.add_argument("--no-restore", action="store_true", help="N>1: skip rank 0's closing copy-engine pass that puts the GPUs' HBM state back (see restore_hbm_state)")
+    ap.add_argument("--no-restore", action="store_true", help="N>1: skip the closing pass that puts the GPUs' HBM state back (see restore_hbm_state)")
     ap.add_argument("--no-clocks", action="store_true", help="ablation only: do not sample NVML clocks while timing")
     ap.add_argument("--clock-period-ms", type=float, default=5.0, help="NVML sampling period during the timed region")
     args = ap.parse_args()
@@ -717,6 +713,17 @@ def main():
         if world == 1 and args.gpus > 1:
             raise SystemExit(f"bench.py: --gpus {args.gpus} needs torchrun (one rank per GPU); see the docstring")
         args.gpus = world
+    if world > 1 and rank == 0 and not args.no_restore and os.environ.get("GPU_PROBE_BENCH_WORKER") != "1":
+        # Rank 0 runs its share of the job in a child, so that THIS process never holds a CUDA context and can
+        # run the closing HBM-state pass when nothing of the job is left on the GPUs (restore_hbm_state).
+        child = subprocess.Popen([sys.executable, os.path.abspath(__file__)] + sys.argv[1:],
+                                 env=dict(os.environ, GPU_PROBE_BENCH_WORKER="1"))
+        for sig in (signal.SIGTERM, signal.SIGINT):
+            signal.signal(sig, lambda s, f: child.send_signal(s))
+        rc = child.wait()
+        if rc == 0:
+            restore_hbm_state(world)
+        sys.exit(rc)
     run_ours(args, rank, local_rank, world)
 
 

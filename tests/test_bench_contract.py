@@ -18,10 +18,23 @@ def _baseline_metric():
         return json.load(f)["metric"]
 
 
-@pytest.mark.parametrize("n", [1, 2, 4, 8])
-def test_committed_bench_lines_keep_the_contract(n):
-    with open(os.path.join(ROOT, "profiles", f"bench_n{n}_r1.json")) as f:
+R2_LINES = {1: "scale_r2_norestore_n1.json", 2: "scale_r2_norestore_n2.json", 4: "scale_r2_norestore_n4.json",
+            8: "scale_r2_restore_n8.json"}
+
+
+@pytest.mark.parametrize("n,name", [(n, f"bench_n{n}_r1.json") for n in (1, 2, 4, 8)] + sorted(R2_LINES.items()))
+def test_committed_bench_lines_keep_the_contract(n, name):
+    with open(os.path.join(ROOT, "profiles", name)) as f:
         d = json.load(f)
+    if "_r2" in name:  # round 2 added: median and max per kernel, the slow-state flag, >= 5 clock samples, a first-hand traffic figure
+        assert d["roofline"]["median_launch_ms"] <= d["roofline"]["max_launch_ms"]
+        assert isinstance(d["roofline"]["slow_state"], bool) and d["clocks"]["samples"] >= 5
+        assert {"median_ms", "max_ms"} <= set(d["kernels"]["triad"]) and {"median_ms", "max_ms"} <= set(d["kernels"]["checksum_u64"])
+        if d["roofline"]["triad_pace_ns"] > 0:
+            assert d["roofline"]["traffic"] in (12815095500, 12849892096)
+        if n > 1:
+            assert all({"slow_state", "triad_ms_median", "triad_ms_max"} <= set(r) for r in d["per_rank"])
+            assert max(r["triad_ms_max"] for r in d["per_rank"]) < 2.5  # no 55 ms calibration inside the timed loop any more
     assert BASE_KEYS <= set(d), sorted(BASE_KEYS - set(d))
     assert d["metric"] == _baseline_metric() and d["unit"] == "GB/s" and d["n_gpus"] == n
     assert d["higher_is_better"] is True and d["scaling"] == "weak" and d["vs_baseline"] is None
@@ -55,3 +68,22 @@ def test_reference_arm_line_keeps_the_contract():
     assert d["impl"] == "reference" and d["metric"] == _baseline_metric() and d["unit"] == "GB/s"
     assert d["cpu_baseline"]["value"] == d["value"] == d["e2e"]["value"]
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0 and d["gpu_launches"] == 0
+
+
+def test_rank0_parent_passes_the_workers_failure_through_and_skips_the_closing_pass(tmp_path):
+    """N > 1: rank 0 runs its share in a child so that the parent, which never holds a CUDA context, can run the
+    closing HBM-state pass once the job is gone.  On a machine without a GPU the child fails loudly (no CPU
+    fallback); the parent must hand that exit status on and must not start the pod command."""
+    env = dict(os.environ, RANK="0", LOCAL_RANK="0", WORLD_SIZE="2", MASTER_ADDR="127.0.0.1", MASTER_PORT="29591")
+    env.pop("GPU_PROBE_BENCH_WORKER", None)
+    try:
+        import torch
+        if torch.cuda.is_available():
+            pytest.skip("GPU present: the N > 1 path is exercised by the scaling jobs")
+    except ImportError:
+        pass
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--gpus", "2", "--steps", "1"], capture_output=True,
+                       text=True, timeout=300, cwd=ROOT, env=env)
+    assert r.returncode != 0
+    assert r.stderr.count("no CUDA device; the probe has no CPU fallback") == 1   # said once, by the worker
+    assert "closing HBM-state pass" not in r.stderr and "{" not in r.stdout

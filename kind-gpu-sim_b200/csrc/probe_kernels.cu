@@ -342,7 +342,12 @@ __device__ __forceinline__ void pace_track_finish(const PaceTrack &trk) {  // on
 //   * a one-way ladder guards against drift inside a launch: over-subscription shows as long
 //     consumer stalls (>= 800 cycles on ~16 % of the tiles instead of 0.3 %); a CTA that sees 5
 //     of them in 64 tiles stops refilling, lets its ring drain and restarts 2 % slower.  It
-//     never speeds up;
+//     never speeds up.  If that did not help -- a second such window -- the CTA stops pacing and
+//     finishes the launch ack-clocked with two tile sets in flight (64 KiB per SM, the unpaced
+//     ring's figure): a launch that starts into an L2 full of another kernel's dirty lines stays
+//     over-subscribed at ANY nearby pace (6080-6210 GB/s for the whole launch); ack-clocked it does
+//     6420-6500, close to the 6630 the ring itself gets there (profiles/paced_mode_r2.jsonl).
+//     Calibration launches keep the plain ladder so that every candidate pace is judged as is;
 //   * every launch also measures itself (PaceTrack: first CTA start to last CTA end on
 //     %globaltimer) and the last CTA leaves the verdict where the HOST can read it without a
 //     synchronisation -- see auto_triad_pace: launches that keep overrunning what their pace
@@ -352,7 +357,7 @@ template <int TILE, int S, bool LANES>
 __global__ void __launch_bounds__(kThreads)
 triad_tma_paced(double *__restrict__ a, const double *__restrict__ b, const double *__restrict__ c, double s, uint64_t n,
                 uint64_t first, uint64_t *__restrict__ out, uint64_t *__restrict__ ws, const ExchangeArgs x, int pace_ns,
-                const PaceTrack trk) {
+                const PaceTrack trk, int mode) {
   static_assert(TILE % (2 * kThreads) == 0, "tile must split into one f64x2 per thread per pass");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   double *sb = reinterpret_cast<double *>(smem_raw);
@@ -388,7 +393,9 @@ triad_tma_paced(double *__restrict__ a, const double *__restrict__ b, const doub
   unsigned long long g_start = 0;
   int pace_cur_ns = pace_ns, bad = 0, win = 0;
   long long pace = (long long)pace_ns * 2;  // cycles; first guess 2 GHz, corrected after 64 tiles
-  bool draining = false;
+  bool draining = false, ack_clocked = false;
+  const bool calibrating = trk.state != nullptr && trk.limit_ns == 0;  // the ladder of paces must be judged as it always was
+  int fallbacks = 0;
   uint64_t grace_until = 0;
   if (tid == 0) {
     c_start = clock64();
@@ -410,7 +417,7 @@ triad_tma_paced(double *__restrict__ a, const double *__restrict__ b, const doub
       }
       if (pj <= j) {  // ring empty: first tile of the kernel, or the drain after a fallback is complete
         draining = false;
-        for (int i = 0; i < S && pj < my_tiles; ++i) issue();
+        for (int i = 0; i < (ack_clocked ? 2 : S) && pj < my_tiles; ++i) issue();
         next_ok = clock64() + pace;
         grace_until = j + 2 * S + 8;  // the start-up burst is not evidence of anything
         bad = win = 0;
@@ -418,10 +425,15 @@ triad_tma_paced(double *__restrict__ a, const double *__restrict__ b, const doub
       t0 = clock64();
     }
     tma::mbar_wait(&full[st], parity);  // (other threads may get here before thread 0 issued: the phase cannot flip without it)
-    if (tid == 0 && !draining && j >= grace_until) {
+    if (tid == 0 && !draining && !ack_clocked && j >= grace_until) {
       if (clock64() - t0 >= kStallCycles) ++bad;
       if (++win == kWindowTiles) {
-        if (bad >= kBadTiles) {  // over-subscribed: drain, then restart one step slower
+        if (bad >= kBadTiles && (mode & 1) && !calibrating && ++fallbacks >= 2) {
+          // second time round: slowing down did not get this CTA out of the over-subscribed regime (typical of a
+          // launch that started into an L2 full of another kernel's dirty lines).  Stop pacing for the rest of the
+          // launch and run ack-clocked with two tile sets in flight -- 64 KiB per SM, the unpaced ring's figure.
+          ack_clocked = true;
+        } else if (bad >= kBadTiles) {  // over-subscribed: drain, then restart one step slower
           draining = true;
           const int step = pace_ns / 50;
           pace = pace * (pace_cur_ns + step) / pace_cur_ns;
@@ -440,7 +452,9 @@ triad_tma_paced(double *__restrict__ a, const double *__restrict__ b, const doub
       if (LANES) lanes_vec(acc, r, t * TILE + 2 * uint64_t(v));
     }
     __syncthreads();  // every thread is done reading slot st
-    if (tid == 0 && !draining && pj < my_tiles && pj > j + 1) {  // (pj == j+1: the ring just emptied -> restart at the loop top)
+    if (tid == 0 && ack_clocked) {
+      while (pj < my_tiles && pj < j + 3) issue();  // tiles j+1, j+2 in flight
+    } else if (tid == 0 && !draining && pj < my_tiles && pj > j + 1) {  // (pj == j+1: the ring just emptied -> restart at the loop top)
       while (clock64() < next_ok) { }
       next_ok += pace;
       const long long now = clock64();
@@ -759,6 +773,10 @@ static int g_auto_checksum = GPU_PROBE_VARIANT_TMA;
 constexpr int kTriadTile = 512, kTriadStages = 4, kTriadCtasPerSm = 2;
 // paced triad: 8 KiB tiles, 4 stages, 2 CTAs/SM (128 KiB of ring per SM; the pace, not the ring, bounds what is in flight)
 constexpr int kPacedTile = 1024, kPacedStages = 4, kPacedCtasPerSm = 2;
+// bit 0: a CTA whose ladder step did not help stops pacing and finishes the launch ack-clocked (see triad_tma_paced).
+// GPU_PROBE_TUNE_PACED_MODE=0 turns that off.  (Spreading the CTAs' refill phases over a pace period and a slower
+// first 48 refills were tried against the dirty-L2 start as well: no effect, profiles/paced_mode_r2.jsonl.)
+constexpr int kPacedMode = 1;
 constexpr int kPacedDefaultNs = 1040;          // explicit VARIANT_TMA_PACED without calibration: a conservative pace
 constexpr uint64_t kPacedMinElems = 1ull << 26;  // below 512 MiB per array the ring kernel is used: nothing to pace
 constexpr int kChecksumTile = 4096, kChecksumStages = 4, kChecksumCtasPerSm = 1;
@@ -813,7 +831,10 @@ static int launch_triad_paced(double *a, const double *b, const double *c, doubl
     const uint64_t tiles_per_cta = (n / kPacedTile + grid - 1) / grid;
     trk.limit_ns = tiles_per_cta * uint64_t(pace_ns) * 104 / 100 + 10000;
   }
-  k<<<grid, kThreads, smem, st>>>(a, b, c, s, n, first, out, ws, x, pace_ns, trk);
+  static const bool tune = getenv("GPU_PROBE_TUNE") != nullptr;  // dev: re-read the knob on every call
+  static int mode = env_or("GPU_PROBE_TUNE_PACED_MODE", kPacedMode);
+  if (tune) mode = env_or("GPU_PROBE_TUNE_PACED_MODE", kPacedMode);
+  k<<<grid, kThreads, smem, st>>>(a, b, c, s, n, first, out, ws, x, pace_ns, trk, mode);
   return launch_rc();
 }
 

@@ -86,3 +86,23 @@ def test_stand_in_neighbour_starts_pinned_and_stops():
         for p in procs:
             p.kill()
             p.wait()
+
+
+def test_pod_runner_beside_reports_both_runs_even_when_the_probe_cannot_start():
+    """Config 5's runner on a machine without a GPU: the placement facts are still reported, both probe runs fail
+    with the device-count exit code (no CPU path), and that code is the runner's own."""
+    try:
+        import torch
+        if torch.cuda.is_available():
+            pytest.skip("GPU present: the measured form is profiles/config5_r2.json")
+    except ImportError:
+        pass
+    import json
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "pod_runner.py"), os.path.join(PODS, "probe-8gpu.yaml"),
+                        "--beside", os.path.join(PODS, "vllm-cpu-pod.yaml"), "--json", "--", "--no-sweep", "--no-p2p",
+                        "--no-sharded"], capture_output=True, text=True, timeout=300)
+    out = json.loads(r.stdout)
+    assert r.returncode == 3 and out["runs"]["alone"]["rc"] == 3 and out["runs"]["beside"]["rc"] == 3
+    assert out["neighbour_lands_on_gpu_workers"] is True and out["neighbour"]["cpus_bound"] == [0, 1, 2, 3]
+    assert out["probe_placement"] == {"nodeSelector_ok": True, "toleration_ok": True}
+    assert out["runs"]["alone"]["triad_GBps_per_gpu"] == {} and "PROBE FAIL rc=3" in out["runs"]["alone"]["verdict"]

@@ -98,7 +98,9 @@ int gpu_probe_triad(double *a, const double *b, const double *c, double s,
  * synchronisation).  After 3 launches in a row that took more than 1.04 x (tiles per CTA x pace)
  * + 10 us -- the memory system sustains less than when the device was calibrated -- AUTO goes
  * back to the ring on that device until it is calibrated again.  Paced AUTO launches that
- * overlap on one device share that record and may trip the guard early; that costs speed only. */
+ * overlap on one device share that record and may trip the guard early; that costs speed only.
+ * The verdict and the addresses behind the guard are remembered per device for the life of the
+ * process; after cudaDeviceReset() call gpu_probe_triad_recalibrate() and calibrate again. */
 int gpu_probe_triad_calibrate(double *a, const double *b, const double *c, uint64_t n,
                               void *stream);
 

@@ -1200,7 +1200,16 @@ int gpu_probe_triad_recalibrate(void) {
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return int(e);
-  if (dev >= 0 && dev < 64) g_pace[dev].pace.store(0, std::memory_order_release);
+  if (dev >= 0 && dev < 64) {
+    PaceDevice &pd = g_pace[dev];
+    std::lock_guard<std::mutex> lock(pd.mu);
+    pd.pace.store(0, std::memory_order_release);
+    // Also forget the addresses: after a cudaDeviceReset() they point at nothing.  The next calibration looks them
+    // up again (when no reset happened the 64 pinned bytes stay where launches still in flight can write them).
+    pd.state.store(nullptr, std::memory_order_release);
+    pd.report_host.store(nullptr, std::memory_order_release);
+    pd.report_dev.store(nullptr, std::memory_order_release);
+  }
   return 0;
 }
 

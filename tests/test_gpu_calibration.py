@@ -39,9 +39,15 @@ for k in range(50):
         paces.append(gpuprobe.triad_pace_ns())
 gpuprobe.checksum_u64(a.data_ptr(), n, 0, out.data_ptr(), ws.data_ptr(), gpuprobe.VARIANT_LDG, st)
 torch.cuda.synchronize()
-print(json.dumps({"verdict": verdict, "host_ms_max": max(host_ms), "paces": paces,
+print(json.dumps({"verdict": verdict, "host_ms_max": max(host_ms), "host_ms_over_1": sum(1 for t in host_ms if t >= 1.0), "paces": paces,
                   "lanes": [int(v) for v in out.cpu().numpy().view(np.uint64)]}))
 '''
+
+
+def never_blocked(got):
+    """A calibration inside a launch costs 55 ms; a bare launch costs microseconds.  The bound is 1 ms per call, with
+    room for two scheduling hiccups of the host among the 50 calls (none of them anywhere near a calibration)."""
+    return got["host_ms_over_1"] <= 2 and got["host_ms_max"] < 10.0
 
 
 def run_case(forced_verdict_ns):
@@ -57,14 +63,14 @@ def test_a_slow_verdict_is_never_retried_behind_the_callers_back(golden):
     """1082 ns is the slow end of the ladder -- the verdict round 1 re-examined on the 8th call."""
     got = run_case(1082)
     assert got["verdict"] == 1082
-    assert got["host_ms_max"] < 1.0, got      # 50 AUTO calls, each a bare asynchronous launch
+    assert never_blocked(got), got            # 50 AUTO calls, each a bare asynchronous launch
     assert got["paces"] == [1082] * 5, got    # behaved launches: the verdict stands, nothing re-calibrated
     assert got["lanes"] == [int(v, 16) for v in golden["pow2_lanes"][27]]
 
 
 def test_a_ring_verdict_keeps_auto_on_the_ring(golden):
     got = run_case(-1)
-    assert got["verdict"] == -1 and got["paces"] == [-1] * 5 and got["host_ms_max"] < 1.0, got
+    assert got["verdict"] == -1 and got["paces"] == [-1] * 5 and never_blocked(got), got
     assert got["lanes"] == [int(v, 16) for v in golden["pow2_lanes"][27]]
 
 
@@ -74,6 +80,6 @@ def test_drift_guard_sends_an_overrunning_device_back_to_the_ring(golden):
     next AUTO call -- still without blocking -- uses the ring.  The bits never change."""
     got = run_case(900)
     assert got["verdict"] == 900
-    assert got["host_ms_max"] < 1.0, got
+    assert never_blocked(got), got
     assert got["paces"] == [-2] * 5, got
     assert got["lanes"] == [int(v, 16) for v in golden["pow2_lanes"][27]]
